@@ -1,0 +1,80 @@
+// lbm_plan.hpp - host-side decomposition of the lattice into slabs (one per GPU),
+// warp-tasks and per-CTA schedules for the persistent neighbour-synchronised engine.
+// Pure C++ (no CUDA): unit-tested on the CPU through the C ABI hooks in lbm_api.cu.
+//
+// Vocabulary
+//   slab      contiguous block of rows owned by one GPU (the reference's per-rank rows,
+//             allocate_rows, d2q9-bgk.c:483-503), stored with one halo row either side.
+//   task      LBM_TASK_CELLS consecutive cells of one row = what one warp updates at a
+//             time (each lane a float4 of 4 cells).  Flat id = local_row * tpr + chunk.
+//   CTA range each persistent CTA owns a contiguous range of flat task ids.
+//   interior  a task whose whole 3x3 task neighbourhood (periodic in x; periodic in y only
+//             for a single slab) is owned by the same CTA: it can be updated for step s+1
+//             as soon as the CTA itself has finished step s.
+//   boundary  every other task: needs the neighbouring CTAs (possibly on the neighbouring
+//             GPU) to have finished step s, both to read their results and to be sure they
+//             no longer read the cells this task overwrites (A/B buffers).
+//   flags     per slab: [0,G) progress of local CTAs, then mirrors of the progress of the
+//             up-neighbour's CTAs that own its first real row, then of the down-neighbour's
+//             CTAs that own its last real row (written by the peer GPU over NVLink).
+#pragma once
+#include <cstdint>
+#include <string>
+#include <vector>
+
+namespace lbm {
+
+constexpr int kTaskCells = 128;   // 32 lanes x float4
+
+struct SlabShape {
+    int rows = 0;        // real rows of this slab
+    int row_start = 0;   // first global row
+};
+
+// The reference's row decomposition (allocate_rows, d2q9-bgk.c:484-496):
+// ny/size rows each, the first ny%size ranks one more.
+SlabShape allocate_rows(int ny, int size, int rank);
+
+// Even contiguous split of `tasks` over `ctas`: CTA b owns [begin(b), begin(b+1)).
+inline int64_t range_begin(int64_t tasks, int ctas, int b) { return tasks * b / ctas; }
+
+struct SlabPlan {
+    int nx = 0, rows = 0, row_start = 0;
+    int rank = 0, size = 1;
+    int tpr = 0;          // tasks per row
+    int num_tasks = 0;
+    int num_ctas = 0;     // G
+    int rows_up = 0, rows_down = 0;   // real rows of the ring neighbours
+    int ctas_up = 0, ctas_down = 0;   // their CTA counts
+    // schedule (CSR style)
+    std::vector<int> task_begin;   // G+1 offsets into task_order
+    std::vector<int> n_interior;   // G: the first n_interior[b] tasks of CTA b are interior
+    std::vector<int> task_order;   // num_tasks flat task ids, interior first per CTA
+    std::vector<int> dep_begin;    // G+1 offsets into deps
+    std::vector<int> deps;         // indices into this slab's flag array
+    // mirrors
+    std::vector<int> up_owners;    // CTAs of the up neighbour owning its FIRST real row (sorted)
+    std::vector<int> down_owners;  // CTAs of the down neighbour owning its LAST real row (sorted)
+    std::vector<int> pub_up;       // G: index in the UP neighbour's flag array this CTA mirrors to, or -1
+    std::vector<int> pub_down;     // G: same for the DOWN neighbour
+    int num_flags = 0;             // G + up_owners.size() + down_owners.size()
+    int accel_local_row = -1;      // local real row that is global row ny-2, else -1
+};
+
+// Owner CTA of flat task `t` for an even split (inverse of range_begin).
+int owner_of(int64_t tasks, int ctas, int64_t t);
+
+// Builds the plan of slab `rank` of `size` for an nx x ny lattice, with `ctas` persistent CTAs
+// on this slab and `ctas_up` / `ctas_down` on the ring neighbours (all equal on a homogeneous
+// box).  Throws std::runtime_error on impossible arguments.
+SlabPlan make_plan(int nx, int ny, int rank, int size, int ctas, int ctas_up, int ctas_down);
+
+// Number of persistent CTAs to use: min(max_resident, number of tasks), at least 1.
+int choose_ctas(int nx, int rows, int max_resident);
+
+// Self-check used by the tests: every task appears exactly once, interior tasks really have
+// all neighbours inside the CTA, every neighbour owner of a boundary task is in deps, mirror
+// indices are consistent between neighbouring plans.  Returns "" or a description.
+std::string validate_plan(const SlabPlan& p);
+
+}  // namespace lbm
