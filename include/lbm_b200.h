@@ -142,6 +142,13 @@ const char* lbm_describe(lbm_ctx* ctx);
  * rows/start of rank r of `size`, and which rank owns global row ny-2.  Host-only. */
 int lbm_allocate_rows(int ny, int size, int rank, int* row_start, int* rows);
 
+/* Host-only self check of the decomposition planner (slabs -> warp-tasks -> per-CTA schedules
+ * and neighbour dependencies) for an nx x ny lattice on `size` GPUs with `ctas` persistent CTAs
+ * each: every task scheduled exactly once, interior tasks have no foreign neighbours, every
+ * neighbour owner is a dependency, mirror-flag indices agree between ring neighbours.
+ * Needs no GPU.  Returns 0 if consistent. */
+int lbm_plan_selftest(int nx, int ny, int size, int ctas);
+
 /* ---- one process per GPU (torchrun-style launch) -------------------------------
  * Rank r of `size` owns slab r on CUDA device `device`.  After creation every rank
  * exports an opaque blob (CUDA IPC handles of its halo rows and progress flags), the

@@ -1,0 +1,277 @@
+"""lattice-boltzmann_b200: B200-native D2Q9-BGK timestep engine.
+
+Python-side mirror of the C ABI in include/lbm_b200.h (ctypes; numpy buffers in, numpy buffers
+out).  The names follow the reference's own (d2q9-bgk.c): params (t_param, :66-87), speeds
+(t_speed, :90-100), accelerate_flow + timestep (:235-339) = `run`, collate (:395-447) =
+`av_vels` / `cells`, write_values (:698-752) = `final_state` / `write_values`.
+
+There is no CPU fallback: importing works anywhere (so that symbol/ABI tests can run on a
+CPU-only box) but constructing `Lattice` without a usable B200 raises `LbmError`.
+
+The directory name contains a hyphen, so import it with
+    importlib.import_module("lattice-boltzmann_b200")
+"""
+import ctypes
+import os
+
+import numpy as np
+
+NSPEEDS = 9
+IPC_BLOB_BYTES = 256
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "liblbm_b200.so")
+
+
+class LbmError(RuntimeError):
+    pass
+
+
+class Params(ctypes.Structure):
+    """lbm_params: the hot-path fields of the reference's t_param (d2q9-bgk.c:66-87)."""
+    _fields_ = [("nx", ctypes.c_int), ("ny", ctypes.c_int), ("max_iters", ctypes.c_int),
+                ("density", ctypes.c_float), ("accel", ctypes.c_float), ("omega", ctypes.c_float),
+                ("obstacle_lines", ctypes.c_int)]
+
+
+class Options(ctypes.Structure):
+    _fields_ = [("strict_fp", ctypes.c_int), ("ctas_per_sm", ctypes.c_int), ("threads_per_cta", ctypes.c_int),
+                ("engine", ctypes.c_int), ("first_device", ctypes.c_int)]
+
+
+_lib = None
+
+# name -> (restype, argtypes); every symbol include/lbm_b200.h declares
+_P = ctypes.c_void_p
+_FP = ctypes.POINTER(ctypes.c_float)
+_IP = ctypes.POINTER(ctypes.c_int)
+SYMBOLS = {
+    "lbm_create": (ctypes.c_int, [ctypes.POINTER(_P), ctypes.POINTER(Params), _P, ctypes.c_int, ctypes.POINTER(Options)]),
+    "lbm_destroy": (None, [_P]),
+    "lbm_run": (ctypes.c_int, [_P, ctypes.c_int]),
+    "lbm_sync": (ctypes.c_int, [_P]),
+    "lbm_get_av_vels": (ctypes.c_int, [_P, _P, ctypes.c_int]),
+    "lbm_get_cells": (ctypes.c_int, [_P, ctypes.POINTER(_P)]),
+    "lbm_set_cells": (ctypes.c_int, [_P, ctypes.POINTER(_P)]),
+    "lbm_get_final_state": (ctypes.c_int, [_P, _P, _P, _P, _P]),
+    "lbm_av_velocity": (ctypes.c_int, [_P, _FP]),
+    "lbm_total_density": (ctypes.c_int, [_P, _FP]),
+    "lbm_abi_version": (ctypes.c_int, []),
+    "lbm_last_error": (ctypes.c_char_p, []),
+    "lbm_device_count": (ctypes.c_int, []),
+    "lbm_steps_done": (ctypes.c_int, [_P]),
+    "lbm_num_slabs": (ctypes.c_int, [_P]),
+    "lbm_slab_rows": (ctypes.c_int, [_P, ctypes.c_int, _IP, _IP]),
+    "lbm_last_run_ms": (ctypes.c_int, [_P, _FP]),
+    "lbm_last_run_launches": (ctypes.c_int, [_P]),
+    "lbm_describe": (ctypes.c_char_p, [_P]),
+    "lbm_allocate_rows": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, ctypes.c_int, _IP, _IP]),
+    "lbm_plan_selftest": (ctypes.c_int, [ctypes.c_int] * 4),
+    "lbm_create_rank": (ctypes.c_int, [ctypes.POINTER(_P), ctypes.POINTER(Params), _P, ctypes.c_int, ctypes.c_int,
+                                       ctypes.c_int, ctypes.POINTER(Options)]),
+    "lbm_rank_export": (ctypes.c_int, [_P, _P]),
+    "lbm_rank_connect": (ctypes.c_int, [_P, _P, _P]),
+    "lbm_inv_free_cells": (ctypes.c_float, [_P]),
+}
+
+
+def load_library(path=None):
+    """Loads liblbm_b200.so (built in-tree by `make` / __graft_entry__.build()). Fails loudly."""
+    global _lib
+    if _lib is not None and path is None:
+        return _lib
+    path = path or LIB_PATH
+    if not os.path.exists(path):
+        raise LbmError(f"{path} not found: build it with `make` (nvcc, sm_100a); there is no fallback")
+    lib = ctypes.CDLL(path)
+    for name, (res, args) in SYMBOLS.items():
+        fn = getattr(lib, name)   # AttributeError if the library lacks a declared symbol
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def _err(lib):
+    return (lib.lbm_last_error() or b"").decode()
+
+
+def allocate_rows(ny, size, rank):
+    """The reference's row decomposition (allocate_rows, d2q9-bgk.c:484-496): (row_start, rows)."""
+    lib = load_library()
+    a, b = ctypes.c_int(), ctypes.c_int()
+    if lib.lbm_allocate_rows(ny, size, rank, ctypes.byref(a), ctypes.byref(b)):
+        raise LbmError(_err(lib))
+    return a.value, b.value
+
+
+def device_count():
+    return load_library().lbm_device_count()
+
+
+def _planes(arr):
+    ptrs = (_P * NSPEEDS)()
+    for k in range(NSPEEDS):
+        ptrs[k] = arr[k].ctypes.data
+    return ptrs
+
+
+class Lattice:
+    """One simulation: the state initialise() builds plus the time loop of main()."""
+
+    def __init__(self, nx, ny, max_iters, density, accel, omega, obstacles, obstacle_lines=-1, ngpus=1,
+                 strict_fp=1, engine=0, ctas_per_sm=0, threads_per_cta=0, first_device=0,
+                 rank=None, size=None, device=None):
+        self.lib = load_library()
+        self.nx, self.ny, self.max_iters = int(nx), int(ny), int(max_iters)
+        self.density = float(density)
+        obst = np.ascontiguousarray(obstacles, dtype=np.int32).reshape(ny, nx)
+        self.obstacles = obst
+        self._prm = Params(nx, ny, max_iters, density, accel, omega, obstacle_lines)
+        self._opt = Options(strict_fp, ctas_per_sm, threads_per_cta, engine, first_device)
+        self._ctx = _P()
+        self.rank_mode = rank is not None
+        if self.rank_mode:
+            rc = self.lib.lbm_create_rank(ctypes.byref(self._ctx), ctypes.byref(self._prm), obst.ctypes.data,
+                                          rank, size, device if device is not None else rank, ctypes.byref(self._opt))
+            self.row_start, self.rows = allocate_rows(ny, size, rank) if not rc else (0, 0)
+        else:
+            rc = self.lib.lbm_create(ctypes.byref(self._ctx), ctypes.byref(self._prm), obst.ctypes.data, ngpus,
+                                     ctypes.byref(self._opt))
+            self.row_start, self.rows = 0, ny
+        if rc:
+            self._ctx = _P()
+            raise LbmError(_err(self.lib))
+
+    # -- life cycle
+    def close(self):
+        if getattr(self, "_ctx", None):
+            self.lib.lbm_destroy(self._ctx)
+            self._ctx = _P()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def _ck(self, rc):
+        if rc:
+            raise LbmError(_err(self.lib))
+
+    # -- hot path
+    def run(self, iters):
+        """`iters` trips of the reference's time loop (d2q9-bgk.c:191-197). Asynchronous."""
+        self._ck(self.lib.lbm_run(self._ctx, int(iters)))
+
+    def sync(self):
+        self._ck(self.lib.lbm_sync(self._ctx))
+
+    # -- results
+    @property
+    def steps_done(self):
+        return self.lib.lbm_steps_done(self._ctx)
+
+    def av_vels(self, n=None):
+        n = self.steps_done if n is None else n
+        out = np.empty(n, np.float32)
+        self._ck(self.lib.lbm_get_av_vels(self._ctx, out.ctypes.data, n))
+        return out
+
+    def cells(self):
+        f = np.empty((NSPEEDS, self.rows, self.nx), np.float32)
+        self._ck(self.lib.lbm_get_cells(self._ctx, _planes(f)))
+        return f
+
+    def set_cells(self, f):
+        f = np.ascontiguousarray(f, np.float32)
+        assert f.shape == (NSPEEDS, self.ny, self.nx)
+        self._ck(self.lib.lbm_set_cells(self._ctx, _planes(f)))
+
+    def final_state(self):
+        """(u_x, u_y, |u|, pressure) as write_values computes them (d2q9-bgk.c:710-741)."""
+        out = [np.empty((self.rows, self.nx), np.float32) for _ in range(4)]
+        self._ck(self.lib.lbm_get_final_state(self._ctx, *[o.ctypes.data for o in out]))
+        return tuple(out)
+
+    def av_velocity(self):
+        v = ctypes.c_float()
+        self._ck(self.lib.lbm_av_velocity(self._ctx, ctypes.byref(v)))
+        return np.float32(v.value)
+
+    def reynolds(self, reynolds_dim, omega):
+        """calc_reynolds (d2q9-bgk.c:675-678), fp32 like the reference."""
+        viscosity = np.float32(1.0) / np.float32(6.0) * (np.float32(2.0) / np.float32(omega) - np.float32(1.0))
+        return np.float32(self.av_velocity() * np.float32(reynolds_dim) / viscosity)
+
+    def total_density(self):
+        v = ctypes.c_float()
+        self._ck(self.lib.lbm_total_density(self._ctx, ctypes.byref(v)))
+        return np.float32(v.value)
+
+    # -- introspection
+    def last_run_ms(self):
+        v = ctypes.c_float()
+        self._ck(self.lib.lbm_last_run_ms(self._ctx, ctypes.byref(v)))
+        return v.value
+
+    def last_run_launches(self):
+        return self.lib.lbm_last_run_launches(self._ctx)
+
+    def describe(self):
+        return (self.lib.lbm_describe(self._ctx) or b"").decode()
+
+    def num_slabs(self):
+        return self.lib.lbm_num_slabs(self._ctx)
+
+    def inv_free_cells(self):
+        return np.float32(self.lib.lbm_inv_free_cells(self._ctx))
+
+    # -- one process per GPU
+    def rank_export(self):
+        blob = ctypes.create_string_buffer(IPC_BLOB_BYTES)
+        self._ck(self.lib.lbm_rank_export(self._ctx, blob))
+        return blob.raw
+
+    def rank_connect(self, blob_up, blob_down):
+        self._ck(self.lib.lbm_rank_connect(self._ctx, blob_up, blob_down))
+
+
+def read_params(path):
+    """The 7-line params file (d2q9-bgk.c:522-528)."""
+    with open(path) as fh:
+        tok = fh.read().split()
+    if len(tok) < 7:
+        raise LbmError(f"could not read param file: {path}")
+    return dict(nx=int(tok[0]), ny=int(tok[1]), max_iters=int(tok[2]), reynolds_dim=int(tok[3]),
+                density=float(np.float32(tok[4])), accel=float(np.float32(tok[5])), omega=float(np.float32(tok[6])))
+
+
+def read_obstacles(path, nx, ny):
+    """Obstacle list "x y 1" (d2q9-bgk.c:628-641) -> (int32 mask[ny, nx], number of lines)."""
+    data = np.loadtxt(path, dtype=np.int64, ndmin=2)
+    if data.shape[1] != 3:
+        raise LbmError("expected 3 values per line in obstacle file")
+    if (data[:, 0] < 0).any() or (data[:, 0] > nx - 1).any():
+        raise LbmError("obstacle x-coord out of range")
+    if (data[:, 1] < 0).any() or (data[:, 1] > ny - 1).any():
+        raise LbmError("obstacle y-coord out of range")
+    if (data[:, 2] != 1).any():
+        raise LbmError("obstacle blocked value should be 1")
+    mask = np.zeros((ny, nx), np.int32)
+    mask[data[:, 1], data[:, 0]] = 1
+    return mask, int(data.shape[0])
+
+
+def from_files(paramfile, obstaclefile, **kw):
+    """`./d2q9-bgk <paramfile> <obstaclefile>` as an object: returns (Lattice, params dict)."""
+    p = read_params(paramfile)
+    mask, lines = read_obstacles(obstaclefile, p["nx"], p["ny"])
+    lat = Lattice(p["nx"], p["ny"], p["max_iters"], p["density"], p["accel"], p["omega"], mask,
+                  obstacle_lines=lines, **kw)
+    return lat, p

@@ -1,0 +1,854 @@
+// lbm_api.cu - implementation of the C ABI in include/lbm_b200.h on top of the sm_100a
+// kernels in lbm_kernels.cuh.  No CPU compute path exists here: every lattice update runs
+// on the device, and creation fails loudly when no CUDA device is usable.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "../../include/lbm_b200.h"
+#include "lbm_kernels.cuh"
+#include "lbm_plan.hpp"
+
+namespace {
+
+thread_local char g_err[1024] = "";
+
+int fail(const char* fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return 1;
+}
+
+#define CK(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess)                                                                     \
+            return fail("%s failed at %s:%d: %s", #call, __FILE__, __LINE__, cudaGetErrorString(e_)); \
+    } while (0)
+
+struct Slab {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev_start = nullptr, ev_stop = nullptr;
+    lbm::SlabPlan plan;
+    lbm::SlabDev dev{};
+    // owned device allocations
+    float* buf[2] = {nullptr, nullptr};
+    unsigned char* mask = nullptr;
+    int* sched = nullptr;          // all schedule arrays in one allocation
+    unsigned* flags = nullptr;
+    double* partials = nullptr;
+    double* tot = nullptr;
+    int* status = nullptr;
+    int* step_ptr = nullptr;       // engine 2: device copy of steps_done
+    float* fields = nullptr;       // scratch for final-state planes (4 * rows * nx)
+    double* scal = nullptr;        // scratch for scalar reductions (2 doubles)
+    // engine 2
+    cudaGraphExec_t graph = nullptr;
+    int graph_steps = 0;
+    int graph_par = -1;
+    // IPC (one-process-per-GPU mode)
+    void* ipc_up_buf[2] = {nullptr, nullptr};
+    void* ipc_down_buf[2] = {nullptr, nullptr};
+    void* ipc_up_flags = nullptr;
+    void* ipc_down_flags = nullptr;
+    int finalized_steps = 0;       // partials already folded into tot
+};
+
+}  // namespace
+
+struct lbm_ctx {
+    lbm_params prm{};
+    lbm_options opt{};
+    int nslabs = 0;          // slabs driven by this process
+    int rank0 = 0;           // global rank of slabs[0]
+    int size = 1;            // total slabs in the ring
+    bool rank_mode = false;  // one process per GPU
+    bool connected = false;
+    std::vector<Slab> slabs;
+    int steps_done = 0;
+    int par = 0;             // buffer holding the current state
+    unsigned base = 0;       // progress-flag base of the next persistent launch
+    int engine = 1;
+    bool strict = true;
+    int threads = 512;
+    int ctas_budget = 0;     // persistent CTAs per slab (before clamping to the task count)
+    int free_cells = 0;      // denominator of av_vels
+    int blocked_cells = 0;
+    float last_ms = 0.f;
+    int last_launches = 0;
+    std::vector<int> obstacles;   // host copy (ny*nx) kept for final-state / diagnostics
+    char desc[512] = "";
+};
+
+namespace {
+
+using lbm::SlabDev;
+
+// ---------------------------------------------------------------- utility kernels
+__global__ void k_fill_uniform(float* buf, long long ps, float w0, float w1, float w2)
+{
+    const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (i >= ps) return;
+    buf[i] = w0;
+#pragma unroll
+    for (int k = 1; k < 5; ++k) buf[k * ps + i] = w1;
+#pragma unroll
+    for (int k = 5; k < 9; ++k) buf[k * ps + i] = w2;
+}
+
+__device__ __forceinline__ bool cell_blocked(const SlabDev& d, int h, int x)
+{
+    return (d.mask[(long long)h * d.mask_pitch + (x >> 3)] >> (x & 7)) & 1u;
+}
+
+// write_values' per-cell fields (d2q9-bgk.c:710-741), same summation order (rho from 0.f, k=0..8).
+__global__ void k_final_state(SlabDev d, int par, float density, float* ux, float* uy, float* u, float* pr)
+{
+    const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    const long long n = (long long)d.rows * d.nx;
+    if (i >= n) return;
+    const int lr = (int)(i / d.nx), x = (int)(i - (long long)lr * d.nx);
+    const float* f = d.buf[par] + (long long)(lr + 1) * d.nx + x;
+    float vx = 0.f, vy = 0.f, vu = 0.f, p;
+    if (cell_blocked(d, lr + 1, x)) {
+        p = __fmul_rn(density, 1.f / 3.f);
+    } else {
+        float q[9];
+#pragma unroll
+        for (int k = 0; k < 9; ++k) q[k] = f[k * d.ps];
+        float rho = 0.f;
+#pragma unroll
+        for (int k = 0; k < 9; ++k) rho = __fadd_rn(rho, q[k]);
+        vx = __fdiv_rn(__fsub_rn(__fadd_rn(__fadd_rn(q[1], q[5]), q[8]), __fadd_rn(__fadd_rn(q[3], q[6]), q[7])), rho);
+        vy = __fdiv_rn(__fsub_rn(__fadd_rn(__fadd_rn(q[2], q[5]), q[6]), __fadd_rn(__fadd_rn(q[4], q[7]), q[8])), rho);
+        vu = __fsqrt_rn(__fadd_rn(__fmul_rn(vx, vx), __fmul_rn(vy, vy)));
+        p = __fmul_rn(rho, 1.f / 3.f);
+    }
+    if (ux) ux[i] = vx;
+    if (uy) uy[i] = vy;
+    if (u) u[i] = vu;
+    if (pr) pr[i] = p;
+}
+
+// out[0] += sum |u| over free cells, out[1] += sum of all populations (double accumulation).
+__global__ void k_diagnostics(SlabDev d, int par, double* out)
+{
+    __shared__ double sh[2][32];
+    const long long n = (long long)d.rows * d.nx;
+    double su = 0.0, sd = 0.0;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const int lr = (int)(i / d.nx), x = (int)(i - (long long)lr * d.nx);
+        const float* f = d.buf[par] + (long long)(lr + 1) * d.nx + x;
+        float q[9];
+#pragma unroll
+        for (int k = 0; k < 9; ++k) q[k] = f[k * d.ps];
+        float rho = 0.f;
+#pragma unroll
+        for (int k = 0; k < 9; ++k) rho = __fadd_rn(rho, q[k]);
+        sd += (double)rho;
+        if (!cell_blocked(d, lr + 1, x)) {
+            const float vx = __fdiv_rn(__fsub_rn(__fadd_rn(__fadd_rn(q[1], q[5]), q[8]), __fadd_rn(__fadd_rn(q[3], q[6]), q[7])), rho);
+            const float vy = __fdiv_rn(__fsub_rn(__fadd_rn(__fadd_rn(q[2], q[5]), q[6]), __fadd_rn(__fadd_rn(q[4], q[7]), q[8])), rho);
+            su += (double)__fsqrt_rn(__fadd_rn(__fmul_rn(vx, vx), __fmul_rn(vy, vy)));
+        }
+    }
+    su = lbm::warp_sum(su);
+    sd = lbm::warp_sum(sd);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane == 0) { sh[0][warp] = su; sh[1][warp] = sd; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double a = 0.0, b = 0.0;
+        for (int w = 0; w < (int)(blockDim.x >> 5); ++w) { a += sh[0][w]; b += sh[1][w]; }
+        atomicAdd(out, a);
+        atomicAdd(out + 1, b);
+    }
+}
+
+// tot[s] = sum over CTAs of partials[s][*], fixed order (deterministic).
+__global__ void k_fold_partials(const double* partials, double* tot, int num_ctas, int s_begin, int s_end)
+{
+    const int s = s_begin + blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (s >= s_end) return;
+    const int lane = threadIdx.x & 31;
+    double a = 0.0;
+    for (int b = lane; b < num_ctas; b += 32) a += partials[(long long)s * num_ctas + b];
+    a = lbm::warp_sum(a);
+    if (lane == 0) tot[s] = a;
+}
+
+}  // namespace
+
+// =========================================================================== slab set-up
+namespace {
+
+const void* persistent_fn(bool strict)
+{
+    return strict ? (const void*)lbm::lbm_persistent_kernel<true> : (const void*)lbm::lbm_persistent_kernel<false>;
+}
+
+int env_int(const char* name, int dflt)
+{
+    const char* v = getenv(name);
+    return (v && *v) ? atoi(v) : dflt;
+}
+
+// Packs rows [row_start-1, row_start+rows] (periodic) of the 0/1 obstacle array to bits.
+std::vector<unsigned char> pack_mask(const int* obst, int nx, int ny, int row_start, int rows, int pitch)
+{
+    std::vector<unsigned char> m((size_t)(rows + 2) * pitch, 0);
+    for (int h = 0; h < rows + 2; ++h) {
+        const int gy = ((row_start - 1 + h) % ny + ny) % ny;
+        for (int x = 0; x < nx; ++x)
+            if (obst[(size_t)gy * nx + x]) m[(size_t)h * pitch + (x >> 3)] |= (unsigned char)(1u << (x & 7));
+    }
+    return m;
+}
+
+void slab_free(Slab& s)
+{
+    if (s.stream == nullptr && s.buf[0] == nullptr) return;
+    cudaSetDevice(s.device);
+    if (s.graph) cudaGraphExecDestroy(s.graph);
+    for (int i = 0; i < 2; ++i) {
+        if (s.ipc_up_buf[i]) cudaIpcCloseMemHandle(s.ipc_up_buf[i]);
+        if (s.ipc_down_buf[i] && s.ipc_down_buf[i] != s.ipc_up_buf[i]) cudaIpcCloseMemHandle(s.ipc_down_buf[i]);
+    }
+    if (s.ipc_up_flags) cudaIpcCloseMemHandle(s.ipc_up_flags);
+    if (s.ipc_down_flags && s.ipc_down_flags != s.ipc_up_flags) cudaIpcCloseMemHandle(s.ipc_down_flags);
+    cudaFree(s.buf[0]); cudaFree(s.buf[1]); cudaFree(s.mask); cudaFree(s.sched); cudaFree(s.flags);
+    cudaFree(s.partials); cudaFree(s.tot); cudaFree(s.status); cudaFree(s.step_ptr); cudaFree(s.fields);
+    cudaFree(s.scal);
+    if (s.ev_start) cudaEventDestroy(s.ev_start);
+    if (s.ev_stop) cudaEventDestroy(s.ev_stop);
+    if (s.stream) cudaStreamDestroy(s.stream);
+    s = Slab();
+}
+
+// Decides engine, CTA shape and the per-slab CTA budget from the device and the options.
+int configure_engine(lbm_ctx* c, int device)
+{
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, device));
+    if (prop.major < 10)
+        return fail("device %d (%s, sm_%d%d) is not a Blackwell-class GPU; this library is built for sm_100a only",
+                    device, prop.name, prop.major, prop.minor);
+    const int sms = prop.multiProcessorCount;
+    c->strict = (c->opt.strict_fp != 2);
+    if (env_int("LBM_FAST_FP", 0)) c->strict = false;
+    c->engine = c->opt.engine ? c->opt.engine : env_int("LBM_ENGINE", 1);
+    if (c->engine != 1 && c->engine != 2) return fail("unknown engine %d", c->engine);
+    if (c->engine == 2 && c->size > 1) return fail("engine 2 (launch per timestep) supports a single slab only");
+    c->threads = c->opt.threads_per_cta ? c->opt.threads_per_cta : env_int("LBM_THREADS", 256);
+    if (c->threads % 32 || c->threads < 32 || c->threads > 512) return fail("threads_per_cta must be a multiple of 32 in [32,512]");
+    int per_sm = c->opt.ctas_per_sm ? c->opt.ctas_per_sm : env_int("LBM_CTAS_PER_SM", 2);
+    int occ = 0;
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, persistent_fn(c->strict), c->threads, 0));
+    if (occ < 1) return fail("persistent kernel does not fit on an SM with %d threads", c->threads);
+    per_sm = std::max(1, std::min(per_sm, occ));
+    c->ctas_budget = sms * per_sm;
+    const int cap = env_int("LBM_MAX_CTAS", 0);
+    if (cap > 0) c->ctas_budget = std::min(c->ctas_budget, cap);
+    return 0;
+}
+
+int slab_create(lbm_ctx* c, Slab& s, int rank, int device, const int* obst)
+{
+    const lbm_params& P = c->prm;
+    s.device = device;
+    CK(cudaSetDevice(device));
+    CK(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
+    CK(cudaEventCreate(&s.ev_start));
+    CK(cudaEventCreate(&s.ev_stop));
+    try {
+        s.plan = lbm::make_plan(P.nx, P.ny, rank, c->size, c->ctas_budget, c->ctas_budget, c->ctas_budget);
+    } catch (const std::exception& e) {
+        return fail("%s", e.what());
+    }
+    const lbm::SlabPlan& pl = s.plan;
+    const long long ps = (long long)(pl.rows + 2) * P.nx;
+    const int G = pl.num_ctas;
+    const int pitch = ((P.nx + 7) / 8 + 15) / 16 * 16;
+
+    for (int i = 0; i < 2; ++i) CK(cudaMalloc(&s.buf[i], sizeof(float) * 9 * ps));
+    CK(cudaMalloc(&s.mask, (size_t)(pl.rows + 2) * pitch));
+    CK(cudaMalloc(&s.flags, sizeof(unsigned) * std::max(pl.num_flags, 1)));
+    CK(cudaMalloc(&s.partials, sizeof(double) * (size_t)std::max(P.max_iters, 1) * G));
+    CK(cudaMalloc(&s.tot, sizeof(double) * std::max(P.max_iters, 1)));
+    CK(cudaMalloc(&s.status, sizeof(int)));
+    CK(cudaMalloc(&s.step_ptr, sizeof(int)));
+    CK(cudaMalloc(&s.scal, sizeof(double) * 2));
+    CK(cudaMemsetAsync(s.flags, 0, sizeof(unsigned) * std::max(pl.num_flags, 1), s.stream));
+    CK(cudaMemsetAsync(s.tot, 0, sizeof(double) * std::max(P.max_iters, 1), s.stream));
+    CK(cudaMemsetAsync(s.status, 0, sizeof(int), s.stream));
+    CK(cudaMemsetAsync(s.step_ptr, 0, sizeof(int), s.stream));
+
+    // schedule arrays, one allocation: task_begin | n_interior | task_order | dep_begin | deps | pub_up | pub_down
+    std::vector<int> h;
+    auto put = [&h](const std::vector<int>& v) { size_t o = h.size(); h.insert(h.end(), v.begin(), v.end()); return o; };
+    const size_t o_tb = put(pl.task_begin), o_ni = put(pl.n_interior), o_to = put(pl.task_order),
+                 o_db = put(pl.dep_begin), o_dp = put(pl.deps), o_pu = put(pl.pub_up), o_pd = put(pl.pub_down);
+    h.push_back(0);
+    CK(cudaMalloc(&s.sched, sizeof(int) * h.size()));
+    CK(cudaMemcpyAsync(s.sched, h.data(), sizeof(int) * h.size(), cudaMemcpyHostToDevice, s.stream));
+
+    const std::vector<unsigned char> m = pack_mask(obst, P.nx, P.ny, pl.row_start, pl.rows, pitch);
+    CK(cudaMemcpyAsync(s.mask, m.data(), m.size(), cudaMemcpyHostToDevice, s.stream));
+
+    // uniform initial state incl. halo rows (d2q9-bgk.c:584-604)
+    const float w0 = P.density * 4.f / 9.f, w1 = P.density / 9.f, w2 = P.density / 36.f;
+    k_fill_uniform<<<(unsigned)((ps + 255) / 256), 256, 0, s.stream>>>(s.buf[0], ps, w0, w1, w2);
+    k_fill_uniform<<<(unsigned)((ps + 255) / 256), 256, 0, s.stream>>>(s.buf[1], ps, w0, w1, w2);
+    CK(cudaGetLastError());
+    CK(cudaStreamSynchronize(s.stream));   // h and m go out of scope
+
+    SlabDev& d = s.dev;
+    d.buf[0] = s.buf[0]; d.buf[1] = s.buf[1];
+    d.mask = s.mask; d.ps = ps; d.nx = P.nx; d.rows = pl.rows; d.tpr = pl.tpr; d.mask_pitch = pitch;
+    d.wrap_y = (c->size == 1);
+    d.accel_lr = pl.accel_local_row;
+    d.omega = P.omega;
+    d.aw1 = P.density * P.accel / 9.f;       // d2q9-bgk.c:237
+    d.aw2 = P.density * P.accel / 36.f;      // d2q9-bgk.c:238
+    d.up_buf[0] = d.up_buf[1] = d.down_buf[0] = d.down_buf[1] = nullptr;
+    d.up_ps = d.down_ps = 0; d.down_rows = pl.rows_down;
+    d.task_begin = s.sched + o_tb; d.n_interior = s.sched + o_ni; d.task_order = s.sched + o_to;
+    d.dep_begin = s.sched + o_db; d.deps = s.sched + o_dp; d.pub_up = s.sched + o_pu; d.pub_down = s.sched + o_pd;
+    d.flags = s.flags; d.up_flags = d.down_flags = nullptr;
+    d.num_ctas = G;
+    d.partials = s.partials; d.tot = s.tot; d.status = s.status;
+    return 0;
+}
+
+int count_cells(lbm_ctx* c, const int* obst)
+{
+    const lbm_params& P = c->prm;
+    const size_t n = (size_t)P.nx * P.ny;
+    c->obstacles.assign(obst, obst + n);
+    int blocked = 0;
+    for (size_t i = 0; i < n; ++i) blocked += (obst[i] != 0);
+    c->blocked_cells = blocked;
+    // the reference divides by nx*ny - <obstacle file LINES> (d2q9-bgk.c:642)
+    c->free_cells = P.nx * P.ny - (P.obstacle_lines >= 0 ? P.obstacle_lines : blocked);
+    if (c->free_cells <= 0) return fail("no free cells (nx*ny - obstacles = %d)", c->free_cells);
+    return 0;
+}
+
+int check_params(const lbm_params* p)
+{
+    if (!p) return fail("params is NULL");
+    if (p->nx < 4 || p->ny < 3) return fail("grid too small: nx=%d ny=%d", p->nx, p->ny);
+    if (p->nx % 4) return fail("nx=%d: this build requires nx to be a multiple of 4 (128-bit lattice accesses); "
+                               "the reference itself assumes nx %% 16 == 0 (d2q9-bgk.c:291)", p->nx);
+    if (p->max_iters < 0) return fail("max_iters < 0");
+    return 0;
+}
+
+void describe(lbm_ctx* c)
+{
+    const Slab& s = c->slabs[0];
+    snprintf(c->desc, sizeof(c->desc),
+             "engine=%s fp=%s slabs=%d/%d ctas/slab=%d threads/cta=%d tasks/slab=%d tasks/row=%d",
+             c->engine == 1 ? "persistent-neighbour-sync" : "launch-per-step-graph", c->strict ? "strict" : "fast",
+             c->nslabs, c->size, s.plan.num_ctas, c->threads, s.plan.num_tasks, s.plan.tpr);
+}
+
+}  // namespace
+
+// =========================================================================== public API
+extern "C" {
+
+int lbm_abi_version(void) { return LBM_ABI_VERSION; }
+const char* lbm_last_error(void) { return g_err; }
+
+int lbm_device_count(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+int lbm_allocate_rows(int ny, int size, int rank, int* row_start, int* rows)
+{
+    if (size < 1 || rank < 0 || rank >= size || ny < 1) return fail("lbm_allocate_rows: bad arguments");
+    const lbm::SlabShape s = lbm::allocate_rows(ny, size, rank);
+    if (row_start) *row_start = s.row_start;
+    if (rows) *rows = s.rows;
+    return 0;
+}
+
+int lbm_plan_selftest(int nx, int ny, int size, int ctas)
+{
+    try {
+        std::vector<lbm::SlabPlan> plans;
+        for (int r = 0; r < size; ++r) {
+            plans.push_back(lbm::make_plan(nx, ny, r, size, ctas, ctas, ctas));
+            const std::string e = lbm::validate_plan(plans.back());
+            if (!e.empty()) return fail("plan of rank %d/%d invalid: %s", r, size, e.c_str());
+        }
+        if (size == 1) return 0;
+        for (int r = 0; r < size; ++r) {   // mirror indices must land in the neighbour's mirror sections
+            const lbm::SlabPlan& p = plans[r];
+            const lbm::SlabPlan& up = plans[(r + 1) % size];
+            const lbm::SlabPlan& dn = plans[(r - 1 + size) % size];
+            if (p.ctas_up != up.num_ctas || p.ctas_down != dn.num_ctas) return fail("rank %d: neighbour CTA counts disagree", r);
+            for (int b = 0; b < p.num_ctas; ++b) {
+                const bool owns_first = lbm::range_begin(p.num_tasks, p.num_ctas, b) < p.tpr;
+                const bool owns_last = lbm::range_begin(p.num_tasks, p.num_ctas, b + 1) > (int64_t)(p.rows - 1) * p.tpr;
+                if ((p.pub_down[b] >= 0) != owns_first || (p.pub_up[b] >= 0) != owns_last)
+                    return fail("rank %d cta %d: publish flags do not match row ownership", r, b);
+                if (owns_first) {   // I am in dn's up_owners section
+                    const int i = p.pub_down[b] - dn.num_ctas;
+                    if (i < 0 || i >= (int)dn.up_owners.size() || dn.up_owners[i] != b) return fail("rank %d cta %d: bad pub_down", r, b);
+                }
+                if (owns_last) {    // I am in up's down_owners section
+                    const int i = p.pub_up[b] - up.num_ctas - (int)up.up_owners.size();
+                    if (i < 0 || i >= (int)up.down_owners.size() || up.down_owners[i] != b) return fail("rank %d cta %d: bad pub_up", r, b);
+                }
+            }
+        }
+    } catch (const std::exception& e) {
+        return fail("%s", e.what());
+    }
+    return 0;
+}
+
+void lbm_destroy(lbm_ctx* c)
+{
+    if (!c) return;
+    for (Slab& s : c->slabs) slab_free(s);
+    delete c;
+}
+
+static int create_common(lbm_ctx** out, const lbm_params* params, const int* obstacles, const lbm_options* opts,
+                         lbm_ctx** cp)
+{
+    if (!out) return fail("out is NULL");
+    *out = nullptr;
+    if (check_params(params)) return 1;
+    if (!obstacles) return fail("obstacles is NULL");
+    if (lbm_device_count() < 1)
+        return fail("no usable CUDA device: liblbm_b200 has no CPU fallback (cudaGetDeviceCount found none)");
+    lbm_ctx* c = new lbm_ctx();
+    c->prm = *params;
+    if (opts) c->opt = *opts;
+    if (count_cells(c, obstacles)) { delete c; return 1; }
+    *cp = c;
+    return 0;
+}
+
+int lbm_create(lbm_ctx** out, const lbm_params* params, const int* obstacles, int ngpus, const lbm_options* opts)
+{
+    lbm_ctx* c = nullptr;
+    if (create_common(out, params, obstacles, opts, &c)) return 1;
+    const int ndev = lbm_device_count();
+    const int first = c->opt.first_device;
+    if (ngpus <= 0) ngpus = env_int("LBM_NGPUS", ndev - first);
+    ngpus = std::min(ngpus, params->ny);
+    if (ngpus < 1 || first < 0 || first + ngpus > ndev || ngpus > LBM_MAX_GPUS) {
+        fail("requested %d GPUs from device %d but %d are visible", ngpus, first, ndev);
+        delete c;
+        return 1;
+    }
+    c->size = c->nslabs = ngpus;
+    c->rank0 = 0;
+    c->slabs.resize(ngpus);
+    int rc = configure_engine(c, first);
+    for (int r = 0; r < ngpus && !rc; ++r) rc = slab_create(c, c->slabs[r], r, first + r, obstacles);
+    // ring links over NVLink peer access (the reference's rank_up / rank_down, d2q9-bgk.c:501-502)
+    for (int r = 0; r < ngpus && !rc && ngpus > 1; ++r) {
+        Slab& s = c->slabs[r];
+        Slab& up = c->slabs[(r + 1) % ngpus];
+        Slab& dn = c->slabs[(r - 1 + ngpus) % ngpus];
+        cudaSetDevice(s.device);
+        for (Slab* o : {&up, &dn}) {
+            int can = 0;
+            cudaDeviceCanAccessPeer(&can, s.device, o->device);
+            if (!can) { rc = fail("device %d cannot access peer %d", s.device, o->device); break; }
+            cudaError_t e = cudaDeviceEnablePeerAccess(o->device, 0);
+            if (e == cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError();
+            else if (e != cudaSuccess) { rc = fail("cudaDeviceEnablePeerAccess: %s", cudaGetErrorString(e)); break; }
+        }
+        SlabDev& d = s.dev;
+        d.up_buf[0] = up.buf[0]; d.up_buf[1] = up.buf[1]; d.up_ps = up.dev.ps; d.up_flags = up.flags;
+        d.down_buf[0] = dn.buf[0]; d.down_buf[1] = dn.buf[1]; d.down_ps = dn.dev.ps; d.down_flags = dn.flags;
+        d.down_rows = dn.plan.rows;
+    }
+    if (rc) { lbm_destroy(c); return 1; }
+    c->connected = true;
+    describe(c);
+    *out = c;
+    return 0;
+}
+
+int lbm_steps_done(const lbm_ctx* c) { return c ? c->steps_done : -1; }
+int lbm_num_slabs(const lbm_ctx* c) { return c ? c->size : -1; }
+const char* lbm_describe(lbm_ctx* c) { return c ? c->desc : ""; }
+float lbm_inv_free_cells(const lbm_ctx* c) { return c ? 1.f / (float)c->free_cells : 0.f; }
+int lbm_last_run_launches(const lbm_ctx* c) { return c ? c->last_launches : -1; }
+
+int lbm_slab_rows(const lbm_ctx* c, int r, int* row_start, int* rows)
+{
+    if (!c || r < 0 || r >= c->size) return fail("lbm_slab_rows: bad slab index");
+    return lbm_allocate_rows(c->prm.ny, c->size, r, row_start, rows);
+}
+
+// ---- engine 2: graph of `gs` timesteps (gs even so the buffer parity returns) ----
+static int build_graph(lbm_ctx* c, Slab& s, int gs)
+{
+    CK(cudaSetDevice(s.device));
+    if (s.graph) { cudaGraphExecDestroy(s.graph); s.graph = nullptr; }
+    const int nw = 8, threads = nw * 32;
+    const int grid = (s.plan.num_tasks + nw - 1) / nw;
+    cudaGraph_t g;
+    CK(cudaStreamBeginCapture(s.stream, cudaStreamCaptureModeThreadLocal));
+    int par = c->par;
+    for (int i = 0; i < gs; ++i) {
+        if (c->strict) lbm::lbm_step_kernel<true><<<grid, threads, 0, s.stream>>>(s.dev, par, s.step_ptr, i, 1);
+        else lbm::lbm_step_kernel<false><<<grid, threads, 0, s.stream>>>(s.dev, par, s.step_ptr, i, 1);
+        par ^= 1;
+    }
+    lbm::lbm_advance_step_kernel<<<1, 1, 0, s.stream>>>(s.step_ptr, gs);
+    CK(cudaStreamEndCapture(s.stream, &g));
+    CK(cudaGraphInstantiate(&s.graph, g, 0));
+    CK(cudaGraphDestroy(g));
+    s.graph_steps = gs;
+    s.graph_par = c->par;
+    return 0;
+}
+
+static int run_engine2(lbm_ctx* c, int iters)
+{
+    Slab& s = c->slabs[0];
+    CK(cudaSetDevice(s.device));
+    const int nw = 8, threads = nw * 32;
+    const int grid = (s.plan.num_tasks + nw - 1) / nw;
+    const int gs = 64;
+    int launches = 0;
+    CK(cudaEventRecord(s.ev_start, s.stream));
+    if (s.dev.accel_lr >= 0) {
+        lbm::lbm_accel_kernel<<<(s.plan.tpr + 3) / 4, 128, 0, s.stream>>>(s.dev, c->par);
+        ++launches;
+    }
+    int remaining = iters;
+    // all but the last step carry the accelerate epilogue for the following step
+    while (remaining - 1 >= gs) {
+        if (!s.graph || s.graph_par != c->par) { if (build_graph(c, s, gs)) return 1; }
+        CK(cudaGraphLaunch(s.graph, s.stream));
+        launches += gs + 1;
+        remaining -= gs;
+    }
+    for (int i = 0; i < remaining; ++i) {
+        const int epi = (i + 1 < remaining) ? 1 : 0;
+        if (c->strict) lbm::lbm_step_kernel<true><<<grid, threads, 0, s.stream>>>(s.dev, c->par, s.step_ptr, i, epi);
+        else lbm::lbm_step_kernel<false><<<grid, threads, 0, s.stream>>>(s.dev, c->par, s.step_ptr, i, epi);
+        c->par ^= 1;
+        ++launches;
+    }
+    if (remaining > 0) { lbm::lbm_advance_step_kernel<<<1, 1, 0, s.stream>>>(s.step_ptr, remaining); ++launches; }
+    CK(cudaGetLastError());
+    CK(cudaEventRecord(s.ev_stop, s.stream));
+    c->last_launches = launches;
+    return 0;
+}
+
+static int run_engine1(lbm_ctx* c, int iters)
+{
+    const void* fn = persistent_fn(c->strict);
+    int launches = 0;
+    for (Slab& s : c->slabs) {
+        CK(cudaSetDevice(s.device));
+        CK(cudaEventRecord(s.ev_start, s.stream));
+        int par0 = c->par, step0 = c->steps_done, it = iters;
+        unsigned base = c->base;
+        void* args[] = {(void*)&s.dev, (void*)&par0, (void*)&step0, (void*)&it, (void*)&base};
+        CK(cudaLaunchCooperativeKernel(fn, dim3(s.plan.num_ctas), dim3(c->threads), args, 0, s.stream));
+        CK(cudaEventRecord(s.ev_stop, s.stream));
+        ++launches;
+    }
+    c->base += (unsigned)iters + 1u;
+    if (iters & 1) c->par ^= 1;
+    c->last_launches = launches;
+    return 0;
+}
+
+int lbm_run(lbm_ctx* c, int iters)
+{
+    if (!c) return fail("ctx is NULL");
+    if (iters < 0) return fail("iters < 0");
+    if (iters == 0) { c->last_launches = 0; return 0; }
+    if (c->steps_done + iters > c->prm.max_iters)
+        return fail("lbm_run: %d + %d steps exceed max_iters=%d", c->steps_done, iters, c->prm.max_iters);
+    if (c->size > 1 && !c->connected) return fail("lbm_run: ring neighbours not connected (call lbm_rank_connect)");
+    const int rc = (c->engine == 1) ? run_engine1(c, iters) : run_engine2(c, iters);
+    if (rc) return rc;
+    c->steps_done += iters;
+    return 0;
+}
+
+int lbm_sync(lbm_ctx* c)
+{
+    if (!c) return fail("ctx is NULL");
+    for (Slab& s : c->slabs) {
+        CK(cudaSetDevice(s.device));
+        CK(cudaStreamSynchronize(s.stream));
+        int st = 0;
+        CK(cudaMemcpy(&st, s.status, sizeof(int), cudaMemcpyDeviceToHost));
+        if (st != 0) return fail("device reported status %d on slab %d (2 = timed out waiting for a neighbouring CTA/GPU)",
+                                 st, (int)(&s - &c->slabs[0]) + c->rank0);
+    }
+    return 0;
+}
+
+int lbm_last_run_ms(lbm_ctx* c, float* ms)
+{
+    if (!c || !ms) return fail("bad arguments");
+    float worst = 0.f;
+    for (Slab& s : c->slabs) {
+        CK(cudaSetDevice(s.device));
+        CK(cudaEventSynchronize(s.ev_stop));
+        float t = 0.f;
+        CK(cudaEventElapsedTime(&t, s.ev_start, s.ev_stop));
+        worst = std::max(worst, t);
+    }
+    *ms = c->last_ms = worst;
+    return 0;
+}
+
+}  // extern "C"
+
+// =========================================================================== results
+namespace {
+
+// Folds the persistent engine's per-CTA partials of steps [finalized, steps_done) into tot[].
+int fold_partials(lbm_ctx* c, Slab& s)
+{
+    if (c->engine != 1 || s.finalized_steps >= c->steps_done) return 0;
+    CK(cudaSetDevice(s.device));
+    const int n = c->steps_done - s.finalized_steps;
+    k_fold_partials<<<(n + 7) / 8, 256, 0, s.stream>>>(s.partials, s.tot, s.plan.num_ctas, s.finalized_steps, c->steps_done);
+    CK(cudaGetLastError());
+    s.finalized_steps = c->steps_done;
+    return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+int lbm_get_av_vels(lbm_ctx* c, float* out, int n)
+{
+    if (!c || !out) return fail("bad arguments");
+    if (n < 0 || n > c->steps_done) return fail("lbm_get_av_vels: n=%d but only %d steps done", n, c->steps_done);
+    if (lbm_sync(c)) return 1;
+    std::vector<double> sum((size_t)n, 0.0), tmp((size_t)n);
+    for (Slab& s : c->slabs) {
+        if (fold_partials(c, s)) return 1;
+        CK(cudaMemcpyAsync(tmp.data(), s.tot, sizeof(double) * n, cudaMemcpyDeviceToHost, s.stream));
+        CK(cudaStreamSynchronize(s.stream));
+        for (int t = 0; t < n; ++t) sum[t] += tmp[t];           // the one reduction over slabs (:445)
+    }
+    if (c->rank_mode) {   // un-normalised local partial; the caller sums across ranks, then scales
+        for (int t = 0; t < n; ++t) out[t] = (float)sum[t];
+    } else {
+        const float r = 1.f / (float)c->free_cells;              // :642
+        for (int t = 0; t < n; ++t) out[t] = (float)sum[t] * r;  // :446
+    }
+    return 0;
+}
+
+int lbm_get_cells(lbm_ctx* c, float* const speeds[LBM_NSPEEDS])
+{
+    if (!c || !speeds) return fail("bad arguments");
+    if (lbm_sync(c)) return 1;
+    const int nx = c->prm.nx;
+    for (Slab& s : c->slabs) {
+        CK(cudaSetDevice(s.device));
+        const size_t row0 = c->rank_mode ? 0 : (size_t)s.plan.row_start;
+        for (int k = 0; k < LBM_NSPEEDS; ++k)
+            CK(cudaMemcpyAsync(speeds[k] + row0 * nx, s.buf[c->par] + k * s.dev.ps + nx,
+                               sizeof(float) * (size_t)s.plan.rows * nx, cudaMemcpyDeviceToHost, s.stream));
+        CK(cudaStreamSynchronize(s.stream));
+    }
+    return 0;
+}
+
+int lbm_set_cells(lbm_ctx* c, const float* const speeds[LBM_NSPEEDS])
+{
+    if (!c || !speeds) return fail("bad arguments");
+    if (c->rank_mode) return fail("lbm_set_cells is not available in one-process-per-GPU mode");
+    if (lbm_sync(c)) return 1;
+    const int nx = c->prm.nx, ny = c->prm.ny;
+    for (Slab& s : c->slabs) {
+        CK(cudaSetDevice(s.device));
+        for (int k = 0; k < LBM_NSPEEDS; ++k) {
+            float* plane = s.buf[c->par] + k * s.dev.ps;
+            const int below = (s.plan.row_start - 1 + ny) % ny, above = (s.plan.row_start + s.plan.rows) % ny;
+            CK(cudaMemcpyAsync(plane, speeds[k] + (size_t)below * nx, sizeof(float) * nx, cudaMemcpyHostToDevice, s.stream));
+            CK(cudaMemcpyAsync(plane + nx, speeds[k] + (size_t)s.plan.row_start * nx,
+                               sizeof(float) * (size_t)s.plan.rows * nx, cudaMemcpyHostToDevice, s.stream));
+            CK(cudaMemcpyAsync(plane + (size_t)(s.plan.rows + 1) * nx, speeds[k] + (size_t)above * nx, sizeof(float) * nx,
+                               cudaMemcpyHostToDevice, s.stream));
+        }
+        CK(cudaStreamSynchronize(s.stream));
+    }
+    return 0;
+}
+
+int lbm_get_final_state(lbm_ctx* c, float* ux, float* uy, float* u, float* pressure)
+{
+    if (!c) return fail("ctx is NULL");
+    if (lbm_sync(c)) return 1;
+    const int nx = c->prm.nx;
+    float* host[4] = {ux, uy, u, pressure};
+    for (Slab& s : c->slabs) {
+        CK(cudaSetDevice(s.device));
+        const size_t n = (size_t)s.plan.rows * nx;
+        if (!s.fields) CK(cudaMalloc(&s.fields, sizeof(float) * 4 * n));
+        float* dv[4];
+        for (int i = 0; i < 4; ++i) dv[i] = host[i] ? s.fields + i * n : nullptr;
+        k_final_state<<<(unsigned)((n + 255) / 256), 256, 0, s.stream>>>(s.dev, c->par, c->prm.density, dv[0], dv[1], dv[2], dv[3]);
+        CK(cudaGetLastError());
+        const size_t row0 = c->rank_mode ? 0 : (size_t)s.plan.row_start;
+        for (int i = 0; i < 4; ++i)
+            if (host[i]) CK(cudaMemcpyAsync(host[i] + row0 * nx, dv[i], sizeof(float) * n, cudaMemcpyDeviceToHost, s.stream));
+        CK(cudaStreamSynchronize(s.stream));
+    }
+    return 0;
+}
+
+static int diagnostics(lbm_ctx* c, double* sum_u, double* sum_rho)
+{
+    if (lbm_sync(c)) return 1;
+    *sum_u = *sum_rho = 0.0;
+    for (Slab& s : c->slabs) {
+        CK(cudaSetDevice(s.device));
+        CK(cudaMemsetAsync(s.scal, 0, sizeof(double) * 2, s.stream));
+        k_diagnostics<<<592, 256, 0, s.stream>>>(s.dev, c->par, s.scal);
+        CK(cudaGetLastError());
+        double h[2];
+        CK(cudaMemcpyAsync(h, s.scal, sizeof(h), cudaMemcpyDeviceToHost, s.stream));
+        CK(cudaStreamSynchronize(s.stream));
+        *sum_u += h[0];
+        *sum_rho += h[1];
+    }
+    return 0;
+}
+
+int lbm_av_velocity(lbm_ctx* c, float* out)
+{
+    if (!c || !out) return fail("bad arguments");
+    double su, sr;
+    if (diagnostics(c, &su, &sr)) return 1;
+    // d2q9-bgk.c:480: tot_u / (float)tot_cells with the TRUE number of unblocked cells
+    const int cells = c->prm.nx * c->prm.ny - c->blocked_cells;
+    *out = c->rank_mode ? (float)su : (float)su / (float)cells;
+    return 0;
+}
+
+int lbm_total_density(lbm_ctx* c, float* out)
+{
+    if (!c || !out) return fail("bad arguments");
+    double su, sr;
+    if (diagnostics(c, &su, &sr)) return 1;
+    *out = (float)sr;
+    return 0;
+}
+
+// =========================================================================== rank mode
+// Blob layout: magic, rank, size, rows, num_ctas, num_flags, plane stride, then three IPC handles.
+struct IpcBlob {
+    unsigned magic;
+    int rank, size, rows, num_ctas, num_flags, nx, pad;
+    long long ps;
+    cudaIpcMemHandle_t buf[2];
+    cudaIpcMemHandle_t flags;
+};
+static_assert(sizeof(IpcBlob) <= LBM_IPC_BLOB_BYTES, "IPC blob too large");
+
+int lbm_create_rank(lbm_ctx** out, const lbm_params* params, const int* obstacles, int rank, int size, int device,
+                    const lbm_options* opts)
+{
+    lbm_ctx* c = nullptr;
+    if (create_common(out, params, obstacles, opts, &c)) return 1;
+    int rc = 0;
+    if (size < 1 || size > params->ny || rank < 0 || rank >= size) rc = fail("bad rank %d / size %d", rank, size);
+    if (!rc && (device < 0 || device >= lbm_device_count())) rc = fail("bad device %d", device);
+    if (!rc) {
+        c->size = size; c->nslabs = 1; c->rank0 = rank; c->rank_mode = true;
+        c->slabs.resize(1);
+        rc = configure_engine(c, device);
+    }
+    if (!rc) rc = slab_create(c, c->slabs[0], rank, device, obstacles);
+    if (rc) { lbm_destroy(c); return 1; }
+    c->connected = (size == 1);
+    describe(c);
+    *out = c;
+    return 0;
+}
+
+int lbm_rank_export(lbm_ctx* c, void* blob)
+{
+    if (!c || !blob || !c->rank_mode) return fail("lbm_rank_export: needs a context made by lbm_create_rank");
+    Slab& s = c->slabs[0];
+    CK(cudaSetDevice(s.device));
+    IpcBlob b;
+    memset(&b, 0, sizeof(b));
+    b.magic = 0x4C424D31u;  // "LBM1"
+    b.rank = c->rank0; b.size = c->size; b.rows = s.plan.rows; b.num_ctas = s.plan.num_ctas;
+    b.num_flags = s.plan.num_flags; b.nx = c->prm.nx; b.ps = s.dev.ps;
+    CK(cudaIpcGetMemHandle(&b.buf[0], s.buf[0]));
+    CK(cudaIpcGetMemHandle(&b.buf[1], s.buf[1]));
+    CK(cudaIpcGetMemHandle(&b.flags, s.flags));
+    memset(blob, 0, LBM_IPC_BLOB_BYTES);
+    memcpy(blob, &b, sizeof(b));
+    return 0;
+}
+
+int lbm_rank_connect(lbm_ctx* c, const void* blob_up, const void* blob_down)
+{
+    if (!c || !c->rank_mode) return fail("lbm_rank_connect: needs a context made by lbm_create_rank");
+    if (c->size == 1) { c->connected = true; return 0; }
+    if (!blob_up || !blob_down) return fail("lbm_rank_connect: NULL blob");
+    Slab& s = c->slabs[0];
+    CK(cudaSetDevice(s.device));
+    IpcBlob up, dn;
+    memcpy(&up, blob_up, sizeof(up));
+    memcpy(&dn, blob_down, sizeof(dn));
+    const int r_up = (c->rank0 + 1) % c->size, r_dn = (c->rank0 - 1 + c->size) % c->size;
+    if (up.magic != 0x4C424D31u || dn.magic != 0x4C424D31u) return fail("lbm_rank_connect: bad blob magic");
+    if (up.rank != r_up || dn.rank != r_dn || up.size != c->size || dn.size != c->size)
+        return fail("lbm_rank_connect: blobs are from ranks %d/%d, expected up=%d down=%d", up.rank, dn.rank, r_up, r_dn);
+    if (up.rows != s.plan.rows_up || dn.rows != s.plan.rows_down || up.num_ctas != s.plan.ctas_up ||
+        dn.num_ctas != s.plan.ctas_down || up.nx != c->prm.nx || dn.nx != c->prm.nx)
+        return fail("lbm_rank_connect: neighbour decomposition differs from the local plan (heterogeneous GPUs?)");
+    const bool same = (r_up == r_dn);   // size == 2: both neighbours are the same process
+    for (int i = 0; i < 2; ++i) {
+        CK(cudaIpcOpenMemHandle(&s.ipc_up_buf[i], up.buf[i], cudaIpcMemLazyEnablePeerAccess));
+        if (same) s.ipc_down_buf[i] = s.ipc_up_buf[i];
+        else CK(cudaIpcOpenMemHandle(&s.ipc_down_buf[i], dn.buf[i], cudaIpcMemLazyEnablePeerAccess));
+    }
+    CK(cudaIpcOpenMemHandle(&s.ipc_up_flags, up.flags, cudaIpcMemLazyEnablePeerAccess));
+    if (same) s.ipc_down_flags = s.ipc_up_flags;
+    else CK(cudaIpcOpenMemHandle(&s.ipc_down_flags, dn.flags, cudaIpcMemLazyEnablePeerAccess));
+    SlabDev& d = s.dev;
+    d.up_buf[0] = (float*)s.ipc_up_buf[0]; d.up_buf[1] = (float*)s.ipc_up_buf[1]; d.up_ps = up.ps;
+    d.down_buf[0] = (float*)s.ipc_down_buf[0]; d.down_buf[1] = (float*)s.ipc_down_buf[1]; d.down_ps = dn.ps;
+    d.up_flags = (unsigned*)s.ipc_up_flags; d.down_flags = (unsigned*)s.ipc_down_flags;
+    d.down_rows = dn.rows;
+    c->connected = true;
+    return 0;
+}
+
+}  // extern "C"
