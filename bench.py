@@ -1,0 +1,357 @@
+#!/usr/bin/env python3
+"""bench.py - GLUPS of the D2Q9-BGK timestep hot path on N B200s, and % of HBM roofline.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+    torchrun ... bench.py --gpus N ...            (one rank per GPU, N > 1)
+
+A "step" is one complete run of the workload's time loop (maxIters timesteps of
+accelerate_flow + propagate + rebound + collision + av_velocity) from device-resident state.
+  N = 1 : workload 1024x1024 (BASELINE.json's single-GPU roofline headline); the JSON line
+          also carries the single-GPU figure of the strong-scaling workload under "also".
+  N > 1 : workload 16384x1024 row-decomposed over the N GPUs (strong scaling), three-population
+          one-row halos pushed over NVLink peer memory from inside the kernel.
+value   = lattice updates of all ranks / device time (CUDA events on the launching stream, max
+          over ranks), in GLUPS.
+e2e     = the same metric through the public C ABI with HOST buffers: lbm_create (mask +
+          schedule upload) + lbm_run + lbm_get_av_vels + lbm_get_cells (downloads) + destroy.
+roofline= algorithmic bytes (72 B per cell update) / kernel time vs MEASURED_PEAKS.json's HBM figure.
+cpu_baseline / --impl reference = the UNMODIFIED reference's OpenMP build (oracle/_ref/ref-omp),
+          timed on this box's host cores on a bounded sample (reduced maxIters; LBM cost per
+          timestep is constant) from its own "Elapsed Compute time" line.
+"""
+import argparse
+import importlib
+import json
+import os
+import re
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+BYTES_PER_UPDATE = 72.0          # 9 fp32 loads + 9 fp32 stores
+FALLBACK_HBM_GBS = 6650.0        # /opt/skills/guides/B200_PROFILING.md, only if MEASURED_PEAKS.json is absent
+REF_OMP = os.path.join(ROOT, "oracle", "_ref", "ref-omp")
+
+
+def hbm_peak():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as fh:
+            return float(json.load(fh)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return FALLBACK_HBM_GBS, "fallback (B200_PROFILING.md)"
+
+
+def grid_files(grid):
+    d = os.path.join(ROOT, "inputs")
+    return os.path.join(d, f"input_{grid}.params"), os.path.join(d, f"obstacles_{grid}.dat")
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device_index=0):
+        self.rows, self.proc, self.idx = [], None, device_index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "200", "-i", str(self.idx)], stdout=subprocess.PIPE, text=True)
+            self.thread = threading.Thread(target=self._pump, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm = sorted(float(r[1]) for r in self.rows if len(r) >= 8 and r[1].replace(".", "").isdigit())
+        mx = [float(r[2]) for r in self.rows if len(r) >= 8 and r[2].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in self.rows if len(r) >= 8 for i in range(4) if r[4 + i].lower() == "active"})
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(self.rows)}
+
+
+# --------------------------------------------------------------------------- CPU reference arm
+def run_reference_sample(grid, iters, threads):
+    """Runs the unmodified reference (OpenMP build) on `grid` with maxIters=iters; returns
+    (compute seconds from its own report, GLUPS)."""
+    if not os.path.exists(REF_OMP):
+        raise RuntimeError(f"{REF_OMP} missing (built by oracle/build_ref.sh where /root/reference exists)")
+    pfile, ofile = grid_files(grid)
+    with open(pfile) as fh:
+        lines = fh.read().split("\n")
+    nx, ny = int(lines[0]), int(lines[1])
+    lines[2] = str(iters)
+    with tempfile.TemporaryDirectory() as tmp:
+        pf = os.path.join(tmp, "sample.params")
+        with open(pf, "w") as fh:
+            fh.write("\n".join(lines))
+        env = dict(os.environ, OMP_NUM_THREADS=str(threads), OMP_PROC_BIND="true", OMP_PLACES="cores")
+        out = subprocess.run([REF_OMP, pf, ofile], cwd=tmp, env=env, check=True, capture_output=True, text=True).stdout
+    secs = float(re.search(r"Elapsed Compute time:\s+([0-9.]+)", out).group(1))
+    return secs, nx * ny * iters / secs / 1e9
+
+
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+def reference_sample_iters(grid, threads, target_s):
+    """Picks maxIters so that one sample takes about target_s seconds on this box."""
+    probe = 100
+    secs, _ = run_reference_sample(grid, probe, threads)
+    return max(probe, int(probe * target_s / max(secs, 1e-3)))
+
+
+def cpu_baseline(grid, target_s=12.0):
+    threads = host_cores()
+    iters = reference_sample_iters(grid, threads, target_s)
+    secs, glups = run_reference_sample(grid, iters, threads)
+    return {"value": glups, "unit": "GLUPS", "cores": threads, "kind": "reference",
+            "sample": f"oracle/_ref/ref-omp (unmodified reference, gcc -O3 -fopenmp, OMP_PROC_BIND=true) on {grid} "
+                      f"with maxIters={iters}: {secs:.2f} s compute"}
+
+
+def reference_arm(args, rank, world):
+    """bench.py --impl reference: the reference's own CPU implementation on this box's host cores."""
+    if rank != 0:
+        return 0
+    grid = args.workload or ("1024x1024" if args.gpus == 1 else "16384x1024")
+    threads = host_cores()
+    try:
+        iters = reference_sample_iters(grid, threads, args.ref_seconds)
+        for _ in range(args.warmup):
+            run_reference_sample(grid, max(iters // 4, 50), threads)
+        secs, updates = 0.0, 0.0
+        for _ in range(args.steps):
+            s, g = run_reference_sample(grid, iters, threads)
+            secs += s
+            updates += g * s
+    except Exception as e:   # the oracle is built in-tree; report rather than crash the driver
+        print(json.dumps({"impl": "reference", "unavailable": str(e)[:200]}))
+        return 0
+    glups = updates / secs
+    nx, ny = (int(v) for v in grid.split("x"))
+    line = {"impl": "reference", "metric": "GLUPS (lattice updates/sec)", "value": glups, "unit": "GLUPS",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": secs / args.steps * 1e3,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": grid, "nx": nx, "ny": ny, "iters_per_step": iters,
+                       "note": "bounded sample: maxIters reduced (LBM cost per timestep is constant)"},
+            "cpu_baseline": {"value": glups, "unit": "GLUPS", "cores": threads, "kind": "reference",
+                             "sample": f"oracle/_ref/ref-omp on {grid}, maxIters={iters} per step, {args.steps} steps"},
+            "e2e": {"value": glups, "unit": "GLUPS", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+    return 0
+
+
+# --------------------------------------------------------------------------- GPU arm
+def flush_l2(torch, scratch):
+    scratch.add_(1)          # 256 MiB read+write > 126 MB L2
+
+
+def time_resident(lbm, torch, grid, iters, steps, warmup, rank, world, dist, scratch):
+    """value leg: state resident in HBM, K steps of `iters` timesteps. Returns dict."""
+    pfile, ofile = grid_files(grid)
+    p = lbm.read_params(pfile)
+    mask, lines = lbm.read_obstacles(ofile, p["nx"], p["ny"])
+    cap = iters * (steps + warmup)
+    common = dict(obstacle_lines=lines)
+    if world > 1:
+        lat = lbm.Lattice(p["nx"], p["ny"], cap, p["density"], p["accel"], p["omega"], mask,
+                          rank=rank, size=world, device=torch.cuda.current_device(), **common)
+        blob = torch.frombuffer(bytearray(lat.rank_export()), dtype=torch.uint8).cuda()
+        blobs = [torch.empty_like(blob) for _ in range(world)]
+        dist.all_gather(blobs, blob)
+        lat.rank_connect(bytes(blobs[(rank + 1) % world].cpu().numpy()), bytes(blobs[(rank - 1) % world].cpu().numpy()))
+    else:
+        lat = lbm.Lattice(p["nx"], p["ny"], cap, p["density"], p["accel"], p["omega"], mask, ngpus=1, **common)
+    lat.sync()
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+
+    for _ in range(warmup):
+        lat.run(iters)
+        lat.sync()
+    barrier()
+    sampler = ClockSampler(torch.cuda.current_device())
+    if rank == 0:
+        sampler.start()
+    dev_ms, launches = 0.0, 0
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        flush_l2(torch, scratch)
+        barrier()
+        lat.run(iters)
+        lat.sync()
+        ms = lat.last_run_ms()
+        if world > 1:
+            t = torch.tensor([ms], device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        dev_ms += ms
+        launches += lat.last_run_launches()
+    barrier()
+    wall = time.perf_counter() - t0
+    clocks = sampler.stop() if rank == 0 else None
+    if world > 1:
+        t = torch.tensor([launches], device="cuda", dtype=torch.int64)
+        dist.all_reduce(t)
+        launches = int(t.item())
+    av = lat.av_vels(min(lat.steps_done, 8))
+    desc = lat.describe()
+    lat.close()
+    updates = float(p["nx"]) * p["ny"] * iters * steps
+    return dict(glups=updates / (dev_ms * 1e-3) / 1e9, ms_per_step=dev_ms / steps, wall_s=wall, launches=launches,
+                clocks=clocks, desc=desc, nx=p["nx"], ny=p["ny"], av0=float(av[0]) if len(av) else None)
+
+
+def time_e2e(lbm, torch, grid, iters, steps, rank, world, dist):
+    """e2e leg: host buffers in, host buffers out, through the public API, every step."""
+    import numpy as np
+    pfile, ofile = grid_files(grid)
+    p = lbm.read_params(pfile)
+    mask, lines = lbm.read_obstacles(ofile, p["nx"], p["ny"])
+    h2d = d2h = 0
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        if world > 1:
+            lat = lbm.Lattice(p["nx"], p["ny"], iters, p["density"], p["accel"], p["omega"], mask, obstacle_lines=lines,
+                              rank=rank, size=world, device=torch.cuda.current_device())
+            blob = torch.frombuffer(bytearray(lat.rank_export()), dtype=torch.uint8).cuda()
+            blobs = [torch.empty_like(blob) for _ in range(world)]
+            dist.all_gather(blobs, blob)
+            lat.rank_connect(bytes(blobs[(rank + 1) % world].cpu().numpy()), bytes(blobs[(rank - 1) % world].cpu().numpy()))
+        else:
+            lat = lbm.Lattice(p["nx"], p["ny"], iters, p["density"], p["accel"], p["omega"], mask, obstacle_lines=lines)
+        lat.run(iters)
+        av = lat.av_vels()
+        f = lat.cells()
+        if world > 1:
+            t = torch.from_numpy(av.astype(np.float64)).cuda()
+            dist.all_reduce(t)               # the one end-of-run sum of per-rank partials (reference :445)
+            av = (t.cpu().numpy() * float(lat.inv_free_cells())).astype(np.float32)
+            dist.barrier()                   # neighbours must be done with my halo rows before I free them
+        a, b = lat.transfer_bytes()
+        h2d += a
+        d2h += b
+        lat.close()
+        assert np.isfinite(av).all() and np.isfinite(f[:, ::64, ::64]).all()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    wall = time.perf_counter() - t0
+    if world > 1:
+        t = torch.tensor([wall, float(h2d), float(d2h)], device="cuda", dtype=torch.float64)
+        tm = t.clone()
+        dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+        dist.all_reduce(t)
+        wall, h2d, d2h = float(tm[0]), float(t[1]), float(t[2])
+    updates = float(p["nx"]) * p["ny"] * iters * steps
+    return dict(glups=updates / wall / 1e9, h2d=int(h2d / steps), d2h=int(d2h / steps))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default=None, help="grid name, e.g. 1024x1024 (default: by --gpus)")
+    ap.add_argument("--iters", type=int, default=0, help="timesteps per step (default: the workload's maxIters)")
+    ap.add_argument("--ref-seconds", type=float, default=12.0, help="CPU seconds per reference sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        return reference_arm(args, rank, world)
+    if args.warmup < 3:
+        args.warmup = 3
+
+    import torch
+    lbm = importlib.import_module("lattice-boltzmann_b200")
+    if not torch.cuda.is_available() or lbm.device_count() < 1:
+        raise SystemExit("bench.py: no CUDA device; the product has no CPU path (use --impl reference for the CPU arm)")
+    dist = None
+    torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", "0")))
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", torch.cuda.current_device()))
+    if world != args.gpus:
+        raise SystemExit(f"bench.py: --gpus {args.gpus} needs {args.gpus} ranks (torchrun), got WORLD_SIZE={world}")
+    scratch = torch.zeros(64 * 1024 * 1024, dtype=torch.float32, device="cuda")
+
+    grid = args.workload or ("1024x1024" if world == 1 else "16384x1024")
+    iters = args.iters or lbm.read_params(grid_files(grid)[0])["max_iters"]
+    res = time_resident(lbm, torch, grid, iters, args.steps, args.warmup, rank, world, dist, scratch)
+    e2e = time_e2e(lbm, torch, grid, iters, max(1, min(args.steps, 3)), rank, world, dist)
+    also = None
+    if world == 1 and not args.workload:
+        big = "16384x1024"
+        r2 = time_resident(lbm, torch, big, 1000, 3, 3, rank, world, dist, scratch)
+        also = {big: {"value": r2["glups"], "unit": "GLUPS", "iters_per_step": 1000, "steps": 3,
+                      "roofline_frac": r2["glups"] * BYTES_PER_UPDATE / hbm_peak()[0],
+                      "note": "single-GPU figure of the strong-scaling workload; 1.2 GB working set, HBM-bound"}}
+    if rank == 0:
+        peak, how = hbm_peak()
+        achieved = res["glups"] * BYTES_PER_UPDATE / world      # GB/s per GPU
+        line = {"metric": "GLUPS (lattice updates/sec)", "value": res["glups"], "unit": "GLUPS", "n_gpus": world,
+                "steps": args.steps, "warmup": args.warmup, "ms_per_step": res["ms_per_step"], "higher_is_better": True,
+                "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": {"workload": grid, "nx": res["nx"], "ny": res["ny"], "iters_per_step": iters,
+                           "parallelism": f"row-slabs x{world}" if world > 1 else "single GPU",
+                           "engine": res["desc"],
+                           "l2": "256 MiB flush between steps; within a step the time loop re-reads its own output"
+                                 " (1024x1024: 75 MB A/B set stays L2-resident by nature; 16384x1024: 1.2 GB, HBM-bound)",
+                           "inputs": "shipped-format params/obstacles regenerated by tools/gen_inputs.py (no RNG)"},
+                "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                             "traffic": None, "peak_source": how,
+                             "note": "achieved = 72 B x cell updates / CUDA-event time of the timestep kernel, per GPU"},
+                "e2e": {"value": e2e["glups"], "unit": "GLUPS", "h2d_bytes_per_step": e2e["h2d"], "d2h_bytes_per_step": e2e["d2h"],
+                        "note": "lbm_create + lbm_run + lbm_get_av_vels + lbm_get_cells + lbm_destroy per step, host buffers"},
+                "gpu_launches": res["launches"], "clocks": res["clocks"], "wall_s_timed_region": res["wall_s"]}
+        if also:
+            line["also"] = also
+        if world == 1 and not args.no_cpu_baseline:
+            try:
+                line["cpu_baseline"] = cpu_baseline(grid, args.ref_seconds)
+            except Exception as e:
+                line["cpu_baseline"] = {"value": None, "unit": "GLUPS", "cores": host_cores(), "kind": "reference",
+                                        "sample": f"failed: {str(e)[:160]}"}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -135,6 +135,9 @@ int lbm_slab_rows(const lbm_ctx* ctx, int r, int* row_start, int* rows);
 int lbm_last_run_ms(lbm_ctx* ctx, float* ms);
 /* Number of kernel launches issued by the most recent lbm_run (all slabs). */
 int lbm_last_run_launches(const lbm_ctx* ctx);
+/* Bytes copied host->device and device->host through this context so far (mask and schedule
+ * uploads, lattice / av_vels / final-state downloads). */
+int lbm_transfer_bytes(const lbm_ctx* ctx, long long* h2d, long long* d2h);
 /* Human-readable description of the engine configuration chosen (static buffer in ctx). */
 const char* lbm_describe(lbm_ctx* ctx);
 

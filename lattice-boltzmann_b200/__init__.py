@@ -63,6 +63,7 @@ SYMBOLS = {
     "lbm_slab_rows": (ctypes.c_int, [_P, ctypes.c_int, _IP, _IP]),
     "lbm_last_run_ms": (ctypes.c_int, [_P, _FP]),
     "lbm_last_run_launches": (ctypes.c_int, [_P]),
+    "lbm_transfer_bytes": (ctypes.c_int, [_P, ctypes.POINTER(ctypes.c_longlong), ctypes.POINTER(ctypes.c_longlong)]),
     "lbm_describe": (ctypes.c_char_p, [_P]),
     "lbm_allocate_rows": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, ctypes.c_int, _IP, _IP]),
     "lbm_plan_selftest": (ctypes.c_int, [ctypes.c_int] * 4),
@@ -209,6 +210,17 @@ class Lattice:
         viscosity = np.float32(1.0) / np.float32(6.0) * (np.float32(2.0) / np.float32(omega) - np.float32(1.0))
         return np.float32(self.av_velocity() * np.float32(reynolds_dim) / viscosity)
 
+    def reynolds_reference_order(self, reynolds_dim, omega):
+        """calc_reynolds with av_velocity summed as the reference does (sequential fp32 over the
+        unblocked cells, jj outer / ii inner, d2q9-bgk.c:454-480) from the device-computed |u| plane:
+        reproduces the reference's printed Reynolds number digit for digit."""
+        _, _, u, _ = self.final_state()
+        free = u[self.obstacles[self.row_start:self.row_start + self.rows] == 0]
+        tot_u = np.cumsum(free, dtype=np.float32)[-1]          # cumsum is a sequential fp32 sum
+        av = np.float32(tot_u / np.float32(free.size))
+        viscosity = np.float32(1.0) / np.float32(6.0) * (np.float32(2.0) / np.float32(omega) - np.float32(1.0))
+        return np.float32(av * np.float32(reynolds_dim) / viscosity)
+
     def total_density(self):
         v = ctypes.c_float()
         self._ck(self.lib.lbm_total_density(self._ctx, ctypes.byref(v)))
@@ -222,6 +234,12 @@ class Lattice:
 
     def last_run_launches(self):
         return self.lib.lbm_last_run_launches(self._ctx)
+
+    def transfer_bytes(self):
+        """(host->device, device->host) bytes copied through this context so far."""
+        a, b = ctypes.c_longlong(), ctypes.c_longlong()
+        self._ck(self.lib.lbm_transfer_bytes(self._ctx, ctypes.byref(a), ctypes.byref(b)))
+        return a.value, b.value
 
     def describe(self):
         return (self.lib.lbm_describe(self._ctx) or b"").decode()

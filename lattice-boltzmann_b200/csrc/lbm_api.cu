@@ -87,6 +87,7 @@ struct lbm_ctx {
     int blocked_cells = 0;
     float last_ms = 0.f;
     int last_launches = 0;
+    long long h2d_bytes = 0, d2h_bytes = 0;   // host<->device traffic issued through this context
     std::vector<int> obstacles;   // host copy (ny*nx) kept for final-state / diagnostics
     char desc[512] = "";
 };
@@ -302,9 +303,11 @@ int slab_create(lbm_ctx* c, Slab& s, int rank, int device, const int* obst)
     h.push_back(0);
     CK(cudaMalloc(&s.sched, sizeof(int) * h.size()));
     CK(cudaMemcpyAsync(s.sched, h.data(), sizeof(int) * h.size(), cudaMemcpyHostToDevice, s.stream));
+    c->h2d_bytes += (long long)(sizeof(int) * h.size());
 
     const std::vector<unsigned char> m = pack_mask(obst, P.nx, P.ny, pl.row_start, pl.rows, pitch);
     CK(cudaMemcpyAsync(s.mask, m.data(), m.size(), cudaMemcpyHostToDevice, s.stream));
+    c->h2d_bytes += (long long)m.size();
 
     // uniform initial state incl. halo rows (d2q9-bgk.c:584-604)
     const float w0 = P.density * 4.f / 9.f, w1 = P.density / 9.f, w2 = P.density / 36.f;
@@ -498,6 +501,14 @@ const char* lbm_describe(lbm_ctx* c) { return c ? c->desc : ""; }
 float lbm_inv_free_cells(const lbm_ctx* c) { return c ? 1.f / (float)c->free_cells : 0.f; }
 int lbm_last_run_launches(const lbm_ctx* c) { return c ? c->last_launches : -1; }
 
+int lbm_transfer_bytes(const lbm_ctx* c, long long* h2d, long long* d2h)
+{
+    if (!c) return fail("ctx is NULL");
+    if (h2d) *h2d = c->h2d_bytes;
+    if (d2h) *d2h = c->d2h_bytes;
+    return 0;
+}
+
 int lbm_slab_rows(const lbm_ctx* c, int r, int* row_start, int* rows)
 {
     if (!c || r < 0 || r >= c->size) return fail("lbm_slab_rows: bad slab index");
@@ -656,6 +667,7 @@ int lbm_get_av_vels(lbm_ctx* c, float* out, int n)
     for (Slab& s : c->slabs) {
         if (fold_partials(c, s)) return 1;
         CK(cudaMemcpyAsync(tmp.data(), s.tot, sizeof(double) * n, cudaMemcpyDeviceToHost, s.stream));
+        c->d2h_bytes += (long long)sizeof(double) * n;
         CK(cudaStreamSynchronize(s.stream));
         for (int t = 0; t < n; ++t) sum[t] += tmp[t];           // the one reduction over slabs (:445)
     }
@@ -679,6 +691,7 @@ int lbm_get_cells(lbm_ctx* c, float* const speeds[LBM_NSPEEDS])
         for (int k = 0; k < LBM_NSPEEDS; ++k)
             CK(cudaMemcpyAsync(speeds[k] + row0 * nx, s.buf[c->par] + k * s.dev.ps + nx,
                                sizeof(float) * (size_t)s.plan.rows * nx, cudaMemcpyDeviceToHost, s.stream));
+        c->d2h_bytes += (long long)LBM_NSPEEDS * sizeof(float) * s.plan.rows * nx;
         CK(cudaStreamSynchronize(s.stream));
     }
     return 0;
@@ -700,6 +713,7 @@ int lbm_set_cells(lbm_ctx* c, const float* const speeds[LBM_NSPEEDS])
                                sizeof(float) * (size_t)s.plan.rows * nx, cudaMemcpyHostToDevice, s.stream));
             CK(cudaMemcpyAsync(plane + (size_t)(s.plan.rows + 1) * nx, speeds[k] + (size_t)above * nx, sizeof(float) * nx,
                                cudaMemcpyHostToDevice, s.stream));
+            c->h2d_bytes += (long long)sizeof(float) * (s.plan.rows + 2) * nx;
         }
         CK(cudaStreamSynchronize(s.stream));
     }
@@ -722,7 +736,10 @@ int lbm_get_final_state(lbm_ctx* c, float* ux, float* uy, float* u, float* press
         CK(cudaGetLastError());
         const size_t row0 = c->rank_mode ? 0 : (size_t)s.plan.row_start;
         for (int i = 0; i < 4; ++i)
-            if (host[i]) CK(cudaMemcpyAsync(host[i] + row0 * nx, dv[i], sizeof(float) * n, cudaMemcpyDeviceToHost, s.stream));
+            if (host[i]) {
+                CK(cudaMemcpyAsync(host[i] + row0 * nx, dv[i], sizeof(float) * n, cudaMemcpyDeviceToHost, s.stream));
+                c->d2h_bytes += (long long)sizeof(float) * n;
+            }
         CK(cudaStreamSynchronize(s.stream));
     }
     return 0;

@@ -3,8 +3,10 @@ the same seeded inputs, against the committed fixtures made by the unmodified re
 through size-independent properties at BASELINE.json's full sizes.
 
 Tolerances: the lattice and the final-state fields are compared BIT-EXACT (strict fp32 mode
-reproduces a plain IEEE build of the reference); av_vels to 2e-6 relative (the reference sums
-|u| sequentially in fp32, the device in a tree with double accumulation); full-length runs
+reproduces a plain IEEE build of the reference); av_vels to 1e-4 relative (the reference sums
+|u| over up to 2M cells SEQUENTIALLY in fp32, which itself carries ~sqrt(N)*eps ~ 1e-5..1e-4 of
+rounding error; the device sums the same bit-identical per-cell values in a tree with double
+accumulation, i.e. closer to the exact sum); full-length runs
 additionally against the reference's shipped known answers at check.py's 1 %.
 """
 import numpy as np
@@ -14,7 +16,7 @@ from helpers import check_py_max_pcnt, load_grid, random_case
 
 pytestmark = pytest.mark.gpu
 
-AV_RTOL = 2e-6
+AV_RTOL = 1e-4
 
 
 def make(lbm, p, mask, lines=-1, iters=None, **kw):
@@ -64,6 +66,7 @@ def test_full_runs_against_shipped_known_answers_and_reference(lbm, golden, grid
         ux, uy, u, pr = lat.final_state()
         av = lat.av_vels()
         re = lat.reynolds(p["reynolds_dim"], p["omega"])
+        re_seq = lat.reynolds_reference_order(p["reynolds_dim"], p["omega"])
     # the reference checker's criterion (check/check.py:136-139): max % difference <= 1
     assert check_py_max_pcnt(shipped["av_vels"], av) <= 1.0
     if "pressure" in shipped:
@@ -71,7 +74,10 @@ def test_full_runs_against_shipped_known_answers_and_reference(lbm, golden, grid
     # the unmodified reference built here with gcc -O3: identical fields after all steps
     assert np.array_equal(pr, full["pressure"]) and np.array_equal(u, full["u"])
     np.testing.assert_allclose(av, full["av_vels"], rtol=AV_RTOL)
-    assert "%.6E" % re == "%.6E" % float(str(full["reynolds"]))
+    # Reynolds number: digit for digit when |u| is summed in the reference's sequential fp32 order;
+    # the device's double-precision tree sum agrees to the rounding error of that fp32 sum.
+    assert "%.12E" % re_seq == str(full["reynolds"])
+    np.testing.assert_allclose(re, float(str(full["reynolds"])), rtol=2e-4)
 
 
 def test_engines_and_split_runs_agree(lbm):

@@ -1,0 +1,120 @@
+"""CPU tests (-m "not gpu"): the C ABI library loads and exports every symbol include/lbm_b200.h
+declares, the host-side planner is consistent, the host driver honours the reference's CLI / error
+conventions, and the product refuses to run without a GPU (no CPU fallback)."""
+import os
+import re
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+EXE = os.path.join(ROOT, "d2q9-bgk")
+
+
+@pytest.fixture(scope="module", autouse=True)
+def built():
+    if not (os.path.exists(EXE) and os.path.exists(os.path.join(ROOT, "lattice-boltzmann_b200", "liblbm_b200.so"))):
+        subprocess.run(["make", "all"], cwd=ROOT, check=True, stdout=subprocess.DEVNULL)
+
+
+def test_library_exports_every_declared_symbol(lbm):
+    with open(os.path.join(ROOT, "include", "lbm_b200.h")) as fh:
+        header = fh.read()
+    header = re.sub(r"/\*.*?\*/", "", header, flags=re.S)
+    declared = set(re.findall(r"\b(lbm_[a-z0-9_]+)\s*\(", header))
+    assert len(declared) >= 25
+    lib = lbm.load_library()
+    for name in declared:
+        assert hasattr(lib, name), f"liblbm_b200.so does not export {name}"
+    assert declared == set(lbm.SYMBOLS), declared ^ set(lbm.SYMBOLS)
+    assert lib.lbm_abi_version() == 1
+
+
+def test_no_cpu_fallback(lbm):
+    if lbm.device_count() > 0:
+        pytest.skip("a GPU is present")
+    with pytest.raises(lbm.LbmError, match="no CPU fallback"):
+        lbm.Lattice(128, 128, 10, 0.1, 0.005, 1.85, np.zeros((128, 128), np.int32))
+
+
+def test_oracle_is_not_reachable_from_the_product():
+    """Nothing shipped may import, link or call anything under oracle/."""
+    for rel in ("lattice-boltzmann_b200/__init__.py", "lattice-boltzmann_b200/csrc/lbm_api.cu",
+                "lattice-boltzmann_b200/csrc/lbm_kernels.cuh", "lattice-boltzmann_b200/csrc/lbm_device.cuh",
+                "lattice-boltzmann_b200/csrc/lbm_plan.cpp", "src/d2q9-bgk.c"):
+        with open(os.path.join(ROOT, rel)) as fh:
+            text = fh.read()
+        assert "oracle" not in text.lower(), f"{rel} mentions the oracle"
+    out = subprocess.run(["ldd", EXE], capture_output=True, text=True).stdout
+    assert "oracle" not in out and "liblbm_b200" in out
+
+
+@pytest.mark.parametrize("ny,size", [(1024, 1), (1024, 3), (1024, 8), (128, 7), (5, 5), (256, 6)])
+def test_allocate_rows_follows_reference_rule(lbm, ny, size):
+    """d2q9-bgk.c:484-496: ny/size rows each, the first ny%size ranks one more, contiguous."""
+    start = 0
+    for r in range(size):
+        s, n = lbm.allocate_rows(ny, size, r)
+        assert s == start and n == ny // size + (1 if r < ny % size else 0)
+        start += n
+    assert start == ny
+
+
+@pytest.mark.parametrize("nx,ny", [(128, 128), (128, 256), (1024, 1024), (16384, 1024), (132, 40), (4, 3), (2048, 7)])
+@pytest.mark.parametrize("size", [1, 2, 3, 8])
+def test_planner_selfcheck(lbm, nx, ny, size):
+    if size > ny:
+        pytest.skip("more slabs than rows")
+    lib = lbm.load_library()
+    for ctas in (1, 5, 148, 296):
+        assert lib.lbm_plan_selftest(nx, ny, size, ctas) == 0, lib.lbm_last_error().decode()
+
+
+def run_exe(*args, cwd=None):
+    return subprocess.run([EXE, *args], capture_output=True, text=True, cwd=cwd)
+
+
+def test_driver_usage_and_die_conventions(tmp_path):
+    """Same messages / exit status as the reference (d2q9-bgk.c:166-168, 516-528, 621-633, 754-764)."""
+    r = run_exe()
+    assert r.returncode == 1 and r.stderr == f"Usage: {EXE} <paramfile> <obstaclefile>\n"
+    r = run_exe("missing.params", "x.dat")
+    assert r.returncode == 1 and "could not open input parameter file: missing.params" in r.stderr
+    assert re.match(r"Error at line \d+ of file .*d2q9-bgk\.c:\n", r.stderr)
+    good = os.path.join(ROOT, "inputs", "input_128x128.params")
+    short = tmp_path / "short.params"
+    short.write_text("128\n128\n")
+    r = run_exe(str(short), "x.dat")
+    assert r.returncode == 1 and "could not read param file: maxIters" in r.stderr
+    r = run_exe(good, str(tmp_path / "nope.dat"))
+    assert r.returncode == 1 and "could not open input obstacles file:" in r.stderr
+    for text, msg in (("1 2\n", "expected 3 values per line in obstacle file"), ("128 0 1\n", "obstacle x-coord out of range"),
+                      ("0 -1 1\n", "obstacle y-coord out of range"), ("3 3 2\n", "obstacle blocked value should be 1")):
+        bad = tmp_path / "bad.dat"
+        bad.write_text(text)
+        r = run_exe(good, str(bad))
+        assert r.returncode == 1 and msg in r.stderr, (text, r.stderr)
+
+
+def test_checker_restatement_matches_reference_checker(tmp_path, golden):
+    """tools/check.py prints and decides exactly like check/check.py (run where the reference exists)."""
+    ref_checker = "/root/reference/check/check.py"
+    if not os.path.exists(ref_checker):
+        pytest.skip("reference tree not present on this box")
+    import oracle_lib
+    g = golden("ref_short_128x128_1000")
+    ny, nx = g["pressure"].shape
+    (tmp_path / "final_state.dat").write_text(oracle_lib.format_final_state(g["ux"], g["uy"], g["u"], g["pressure"], g["obstacles"]))
+    (tmp_path / "av_vels.dat").write_text(oracle_lib.format_av_vels(g["av_vels"]))
+    bad_p = g["pressure"].copy()
+    bad_p[5, 5] *= 1.05
+    (tmp_path / "final_state_bad.dat").write_text(oracle_lib.format_final_state(g["ux"], g["uy"], g["u"], bad_p, g["obstacles"]))
+    for fs, expect in (("final_state.dat", 0), ("final_state_bad.dat", 1)):
+        args = ["--ref-av-vels-file", str(tmp_path / "av_vels.dat"), "--ref-final-state-file", str(tmp_path / "final_state.dat"),
+                "--av-vels-file", str(tmp_path / "av_vels.dat"), "--final-state-file", str(tmp_path / fs)]
+        a = subprocess.run([sys.executable, ref_checker, *args], capture_output=True, text=True)
+        b = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "check.py"), *args], capture_output=True, text=True)
+        assert a.returncode == b.returncode == expect
+        assert a.stdout == b.stdout

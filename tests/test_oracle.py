@@ -1,0 +1,92 @@
+"""CPU tests (-m "not gpu"): pin the oracle restatement (oracle/lbm_oracle.c) to the reference.
+
+ (1) bit-for-bit against outputs of the UNMODIFIED reference (tests/golden/ref_short_*.npz,
+     made by tests/golden/make_golden.py from oracle/_ref/ref-serial), and
+ (2) against the reference's shipped known answers check/<grid>.dat (tests/golden/shipped_*.npz)
+     at the reference checker's 1 % rule on a full-length run.
+"""
+import os
+
+import numpy as np
+import pytest
+
+from helpers import check_py_max_pcnt, load_grid, random_case
+
+
+def run_oracle(oracle, grid, steps):
+    p, mask, lines = load_grid(grid)
+    f, tot = oracle.run(p["nx"], p["ny"], steps, p["density"], p["accel"], p["omega"], mask)
+    av = oracle.scale_av_vels(tot, p["nx"], p["ny"], lines)
+    return p, mask, f, av
+
+
+@pytest.mark.parametrize("grid,steps", [("128x128", 1000), ("128x256", 1000)])
+def test_oracle_bit_identical_to_unmodified_reference(oracle, golden, grid, steps):
+    g = golden(f"ref_short_{grid}_{steps}")
+    p, mask, f, av = run_oracle(oracle, grid, steps)
+    ux, uy, u, pr = oracle.final_state(f, p["density"], mask)
+    assert np.array_equal(av, g["av_vels"])
+    for name, got in (("ux", ux), ("uy", uy), ("u", u), ("pressure", pr)):
+        assert np.array_equal(got, g[name]), name
+    assert np.array_equal(mask.astype(np.uint8), g["obstacles"])
+    assert "%.12E" % oracle.reynolds(f, p["reynolds_dim"], p["omega"], mask) == str(g["reynolds"])
+
+
+def test_oracle_large_grid_prefix_matches_reference(oracle, golden):
+    g = golden("ref_short_1024x1024_200")
+    p, mask, f, av = run_oracle(oracle, "1024x1024", 40)
+    assert np.array_equal(av, g["av_vels"][:40])
+
+
+def test_oracle_full_run_passes_reference_checker_rule(oracle, golden):
+    """Full 128x128 run (40 000 steps) vs the reference's shipped known answers, check.py's rule."""
+    shipped, full = golden("shipped_128x128"), golden("ref_full_128x128")
+    p, mask, f, av = run_oracle(oracle, "128x128", 40000)
+    _, _, _, pr = oracle.final_state(f, p["density"], mask)
+    assert check_py_max_pcnt(shipped["av_vels"], av) <= 1.0
+    assert check_py_max_pcnt(shipped["pressure"], pr) <= 1.0
+    assert np.array_equal(av, full["av_vels"]) and np.array_equal(pr, full["pressure"])
+
+
+@pytest.mark.parametrize("ranks", [2, 3, 5, 8])
+def test_oracle_rank_decomposition_equals_single_domain(oracle, ranks):
+    """The reference's row decomposition + halo exchange (emulated ranks) reproduces the single
+    domain bit for bit, including the periodic top/bottom link of 128x256."""
+    p, mask, lines = load_grid("128x256")
+    f1, t1 = oracle.run(p["nx"], p["ny"], 60, p["density"], p["accel"], p["omega"], mask)
+    fr, tr = oracle.run(p["nx"], p["ny"], 60, p["density"], p["accel"], p["omega"], mask, ranks=ranks)
+    assert np.array_equal(f1, fr)
+    np.testing.assert_allclose(tr, t1, rtol=1e-5)
+
+
+def test_oracle_invariants(oracle):
+    mask, f0 = random_case(64, 48, seed=3)
+    m0 = oracle.total_density(f0)
+    f1, tot = oracle.timestep(f0, 1.85, mask)
+    assert abs(float(oracle.total_density(f1)) - float(m0)) / float(m0) < 1e-5      # mass is conserved
+    # obstacle cells only permute their pulled values (bounce-back): recompute by hand
+    ys, xs = np.nonzero(mask)
+    y, x = int(ys[0]), int(xs[0])
+    ny, nx = mask.shape
+    pulled = [f0[0, y, x], f0[1, y, (x - 1) % nx], f0[2, (y - 1) % ny, x], f0[3, y, (x + 1) % nx], f0[4, (y + 1) % ny, x],
+              f0[5, (y - 1) % ny, (x - 1) % nx], f0[6, (y - 1) % ny, (x + 1) % nx], f0[7, (y + 1) % ny, (x + 1) % nx],
+              f0[8, (y + 1) % ny, (x - 1) % nx]]
+    opp = [0, 3, 4, 1, 2, 7, 8, 5, 6]
+    assert all(f1[k, y, x] == pulled[opp[k]] for k in range(9))
+    # accelerate_flow touches only row ny-2 and conserves mass there
+    fa = oracle.accelerate_flow(f0, 0.1, 0.005, mask)
+    assert np.array_equal(np.delete(fa, ny - 2, axis=1), np.delete(f0, ny - 2, axis=1))
+    np.testing.assert_allclose(fa[:, ny - 2].sum(), f0[:, ny - 2].sum(), rtol=1e-5)
+    assert np.array_equal(fa[:, ny - 2][:, mask[ny - 2] == 1], f0[:, ny - 2][:, mask[ny - 2] == 1])
+
+
+def test_inputs_match_generator_and_reference_if_present():
+    import subprocess, sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    for g, n in (("128x128", 512), ("128x256", 640), ("1024x1024", 5120), ("16384x1024", 36864)):
+        with open(os.path.join(root, "inputs", f"obstacles_{g}.dat")) as fh:
+            assert sum(1 for _ in fh) == n          # line counts incl. duplicated corners
+    if os.path.isdir("/root/reference"):
+        r = subprocess.run([sys.executable, os.path.join(root, "tools", "gen_inputs.py"), "--verify", "/root/reference",
+                            "--out", os.path.join(root, "inputs")], capture_output=True, text=True)
+        assert r.returncode == 0, r.stdout
