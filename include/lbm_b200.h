@@ -152,6 +152,11 @@ int lbm_allocate_rows(int ny, int size, int rank, int* row_start, int* rows);
  * Needs no GPU.  Returns 0 if consistent. */
 int lbm_plan_selftest(int nx, int ny, int size, int ctas);
 
+/* Device self check of the kernel's exact division / square-root fast paths: evaluates them on
+ * 2*n hashed operand pairs (whole accepted range, and LBM-like magnitudes) and counts results that
+ * differ in any bit from the IEEE-rounded intrinsics.  *mismatches must come back 0. */
+int lbm_selftest_math(long long n, long long seed, long long* mismatches);
+
 /* ---- one process per GPU (torchrun-style launch) -------------------------------
  * Rank r of `size` owns slab r on CUDA device `device`.  After creation every rank
  * exports an opaque blob (CUDA IPC handles of its halo rows and progress flags), the

@@ -67,6 +67,7 @@ SYMBOLS = {
     "lbm_describe": (ctypes.c_char_p, [_P]),
     "lbm_allocate_rows": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, ctypes.c_int, _IP, _IP]),
     "lbm_plan_selftest": (ctypes.c_int, [ctypes.c_int] * 4),
+    "lbm_selftest_math": (ctypes.c_int, [ctypes.c_longlong, ctypes.c_longlong, ctypes.POINTER(ctypes.c_longlong)]),
     "lbm_create_rank": (ctypes.c_int, [ctypes.POINTER(_P), ctypes.POINTER(Params), _P, ctypes.c_int, ctypes.c_int,
                                        ctypes.c_int, ctypes.POINTER(Options)]),
     "lbm_rank_export": (ctypes.c_int, [_P, _P]),
@@ -103,6 +104,15 @@ def allocate_rows(ny, size, rank):
     if lib.lbm_allocate_rows(ny, size, rank, ctypes.byref(a), ctypes.byref(b)):
         raise LbmError(_err(lib))
     return a.value, b.value
+
+
+def selftest_math(n=1 << 26, seed=1):
+    """Mismatches (must be 0) between the kernel's exact div/sqrt fast paths and the IEEE intrinsics."""
+    lib = load_library()
+    bad = ctypes.c_longlong(-1)
+    if lib.lbm_selftest_math(n, seed, ctypes.byref(bad)):
+        raise LbmError(_err(lib))
+    return bad.value
 
 
 def device_count():

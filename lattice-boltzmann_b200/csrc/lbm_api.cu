@@ -189,6 +189,39 @@ __global__ void k_fold_partials(const double* partials, double* tot, int num_cta
     if (lane == 0) tot[s] = a;
 }
 
+// Brute-force check of the exact fast paths in lbm_device.cuh against the IEEE intrinsics.
+// Operands are hashed bit patterns: mode 0 spans the whole accepted range (and a little beyond it,
+// where the range tests must reject), mode 1 concentrates on LBM-like magnitudes (rho ~ 0.1).
+__device__ __forceinline__ unsigned mix32(unsigned long long x)
+{
+    x ^= x >> 33; x *= 0xff51afd7ed558ccdULL; x ^= x >> 33; x *= 0xc4ceb9fe1a85ec53ULL; x ^= x >> 33;
+    return (unsigned)x;
+}
+
+__global__ void k_selftest_math(unsigned long long n, unsigned long long seed, int mode, unsigned long long* bad)
+{
+    unsigned long long local = 0;
+    for (unsigned long long i = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x; i < n;
+         i += (unsigned long long)gridDim.x * blockDim.x) {
+        const unsigned h1 = mix32(seed + 3 * i), h2 = mix32(seed + 3 * i + 1), h3 = mix32(seed + 3 * i + 2);
+        unsigned eb, ea;
+        if (mode == 0) { eb = 115u + h3 % 25u; ea = 26u + (h3 >> 8) % 126u; }      // straddles both range limits
+        else           { eb = 121u + h3 % 5u;  ea = 90u + (h3 >> 8) % 34u; }
+        const float b = __uint_as_float((eb << 23) | (h1 & 0x7fffffu));
+        float a = __uint_as_float((h2 & 0x80000000u) | (ea << 23) | (h2 & 0x7fffffu));
+        if ((h3 >> 20) % 61u == 0u) a = 0.f;
+        if (lbm::div_den_ok(b) && lbm::div_num_ok(a)) {
+            const float q = lbm::div_fast(a, b, lbm::rcp_refined(b));
+            if (__float_as_uint(q) != __float_as_uint(__fdiv_rn(a, b))) ++local;
+        }
+        const float x = fabsf(a) * ((h3 & 1u) ? 1.f : b);
+        if (lbm::sqrt_arg_ok(x)) {
+            if (__float_as_uint(lbm::sqrt_fast(x)) != __float_as_uint(__fsqrt_rn(x))) ++local;
+        }
+    }
+    if (local) atomicAdd(bad, local);
+}
+
 }  // namespace
 
 // =========================================================================== slab set-up
@@ -279,6 +312,9 @@ int slab_create(lbm_ctx* c, Slab& s, int rank, int device, const int* obst)
     }
     const lbm::SlabPlan& pl = s.plan;
     const long long ps = (long long)(pl.rows + 2) * P.nx;
+    if (9 * ps >= (1LL << 32))
+        return fail("slab of %d rows x %d cells is too large for 32-bit lattice offsets (9*(rows+2)*nx must be < 2^32); "
+                    "use more GPUs", pl.rows, P.nx);
     const int G = pl.num_ctas;
     const int pitch = ((P.nx + 7) / 8 + 15) / 16 * 16;
 
@@ -295,10 +331,15 @@ int slab_create(lbm_ctx* c, Slab& s, int rank, int device, const int* obst)
     CK(cudaMemsetAsync(s.status, 0, sizeof(int), s.stream));
     CK(cudaMemsetAsync(s.step_ptr, 0, sizeof(int), s.stream));
 
-    // schedule arrays, one allocation: task_begin | n_interior | task_order | dep_begin | deps | pub_up | pub_down
+    // schedule arrays, one allocation: task_order as (row, chunk) pairs first (8-byte aligned), then
+    // task_begin | n_interior | dep_begin | deps | pub_up | pub_down
     std::vector<int> h;
     auto put = [&h](const std::vector<int>& v) { size_t o = h.size(); h.insert(h.end(), v.begin(), v.end()); return o; };
-    const size_t o_tb = put(pl.task_begin), o_ni = put(pl.n_interior), o_to = put(pl.task_order),
+    std::vector<int> pairs;
+    pairs.reserve(2 * pl.task_order.size());
+    for (int t : pl.task_order) { pairs.push_back(t / pl.tpr); pairs.push_back(t % pl.tpr); }
+    const size_t o_to = put(pairs);
+    const size_t o_tb = put(pl.task_begin), o_ni = put(pl.n_interior),
                  o_db = put(pl.dep_begin), o_dp = put(pl.deps), o_pu = put(pl.pub_up), o_pd = put(pl.pub_down);
     h.push_back(0);
     CK(cudaMalloc(&s.sched, sizeof(int) * h.size()));
@@ -326,7 +367,7 @@ int slab_create(lbm_ctx* c, Slab& s, int rank, int device, const int* obst)
     d.aw2 = P.density * P.accel / 36.f;      // d2q9-bgk.c:238
     d.up_buf[0] = d.up_buf[1] = d.down_buf[0] = d.down_buf[1] = nullptr;
     d.up_ps = d.down_ps = 0; d.down_rows = pl.rows_down;
-    d.task_begin = s.sched + o_tb; d.n_interior = s.sched + o_ni; d.task_order = s.sched + o_to;
+    d.task_begin = s.sched + o_tb; d.n_interior = s.sched + o_ni; d.task_order = (const int2*)(s.sched + o_to);
     d.dep_begin = s.sched + o_db; d.deps = s.sched + o_dp; d.pub_up = s.sched + o_pu; d.pub_down = s.sched + o_pd;
     d.flags = s.flags; d.up_flags = d.down_flags = nullptr;
     d.num_ctas = G;
@@ -424,6 +465,22 @@ int lbm_plan_selftest(int nx, int ny, int size, int ctas)
     } catch (const std::exception& e) {
         return fail("%s", e.what());
     }
+    return 0;
+}
+
+int lbm_selftest_math(long long n, long long seed, long long* mismatches)
+{
+    if (!mismatches || n < 0) return fail("bad arguments");
+    if (lbm_device_count() < 1) return fail("no usable CUDA device");
+    unsigned long long* d = nullptr;
+    CK(cudaMalloc(&d, sizeof(unsigned long long)));
+    CK(cudaMemset(d, 0, sizeof(unsigned long long)));
+    for (int mode = 0; mode < 2; ++mode) k_selftest_math<<<1184, 256>>>((unsigned long long)n, (unsigned long long)seed, mode, d);
+    CK(cudaGetLastError());
+    unsigned long long h = 0;
+    CK(cudaMemcpy(&h, d, sizeof(h), cudaMemcpyDeviceToHost));
+    CK(cudaFree(d));
+    *mismatches = (long long)h;
     return 0;
 }
 

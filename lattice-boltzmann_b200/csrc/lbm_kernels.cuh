@@ -4,31 +4,38 @@
 
 namespace lbm {
 
+// Geometry of one warp-task for one lane.  All lattice offsets are 32-bit ELEMENT offsets from
+// the buffer base (lbm_create guarantees 9*ps < 2^32), so an address costs one IMAD.WIDE.
 struct TaskGeom {
-    int lr, x0, xc, h, hs, hn;
+    int lr, x0, xc;
+    unsigned rc, rs, rn;     // element offsets of (row, xc), (south row, xc), (north row, xc) in plane 0
+    unsigned wc, ws, wn;     // same rows at the west neighbour column of this lane's first cell
+    unsigned ec, es, en;     // same rows at the east neighbour column of this lane's last cell
     bool active, need_w, need_e;
-    int xw, xe;
 };
 
-__device__ __forceinline__ TaskGeom task_geom(const SlabDev& d, int task, int lane)
+__device__ __forceinline__ TaskGeom task_geom(const SlabDev& d, int2 td, int lane)
 {
     TaskGeom g;
-    g.lr = task / d.tpr;
-    const int chunk = task - g.lr * d.tpr;
-    g.x0 = chunk * 128 + lane * 4;
+    g.lr = td.x;
+    g.x0 = td.y * 128 + lane * 4;
     g.active = g.x0 < d.nx;
     g.xc = g.active ? g.x0 : 0;            // inactive lanes (ragged last chunk) shadow x=0, never store
-    g.h = g.lr + 1;                        // row index in the haloed layout
-    g.hs = g.h - 1;
-    g.hn = g.h + 1;
+    const int h = g.lr + 1;                // row index in the haloed layout
+    int hs = h - 1, hn = h + 1;
     if (d.wrap_y) {                        // single slab: periodic in y inside the slab
-        if (g.lr == 0) g.hs = d.rows;
-        if (g.lr == d.rows - 1) g.hn = 1;
+        if (g.lr == 0) hs = d.rows;
+        if (g.lr == d.rows - 1) hn = 1;
     }
     g.need_w = (lane == 0);
     g.need_e = (lane == 31) || (g.xc + 4 >= d.nx);
-    g.xw = (g.xc == 0) ? d.nx - 1 : g.xc - 1;          // d2q9-bgk.c:289
-    g.xe = (g.xc + 4 >= d.nx) ? 0 : g.xc + 4;          // d2q9-bgk.c:288
+    const unsigned nx = (unsigned)d.nx;
+    const unsigned xw = (g.xc == 0) ? nx - 1u : (unsigned)g.xc - 1u;          // d2q9-bgk.c:289
+    const unsigned xe = (g.xc + 4 >= d.nx) ? 0u : (unsigned)g.xc + 4u;        // d2q9-bgk.c:288
+    const unsigned bc = (unsigned)h * nx, bs = (unsigned)hs * nx, bn = (unsigned)hn * nx;
+    g.rc = bc + g.xc; g.rs = bs + g.xc; g.rn = bn + g.xc;
+    g.wc = bc + xw;   g.ws = bs + xw;   g.wn = bn + xw;
+    g.ec = bc + xe;   g.es = bs + xe;   g.en = bn + xe;
     return g;
 }
 
@@ -36,37 +43,36 @@ __device__ __forceinline__ TaskGeom task_geom(const SlabDev& d, int task, int la
 // optional accelerate_flow epilogue for the NEXT step on row ny-2, store, halo push to the
 // ring neighbours, and returns the lane's sum of |u| over its fluid cells.
 template <bool S>
-__device__ __forceinline__ float process_task(const SlabDev& d, int par, int task, int lane, bool epilogue_accel)
+__device__ __forceinline__ float process_task(const SlabDev& d, int par, int2 td, int lane, bool epilogue_accel)
 {
-    const TaskGeom g = task_geom(d, task, lane);
+    const TaskGeom g = task_geom(d, td, lane);
     const float* __restrict__ src = d.buf[par];
     float* __restrict__ dst = d.buf[par ^ 1];
-    const long long ps = d.ps;
-    const long long rc = (long long)g.h * d.nx, rs = (long long)g.hs * d.nx, rn = (long long)g.hn * d.nx;
+    const unsigned ps = (unsigned)d.ps;
 
     // ---- 9 aligned 128-bit loads (all issued before first use)
-    const float4 c0 = ld_cg4(src + 0 * ps + rc + g.xc);
-    const float4 c1 = ld_cg4(src + 1 * ps + rc + g.xc);
-    const float4 c3 = ld_cg4(src + 3 * ps + rc + g.xc);
-    const float4 s2 = ld_cg4(src + 2 * ps + rs + g.xc);
-    const float4 s5 = ld_cg4(src + 5 * ps + rs + g.xc);
-    const float4 s6 = ld_cg4(src + 6 * ps + rs + g.xc);
-    const float4 n4 = ld_cg4(src + 4 * ps + rn + g.xc);
-    const float4 n7 = ld_cg4(src + 7 * ps + rn + g.xc);
-    const float4 n8 = ld_cg4(src + 8 * ps + rn + g.xc);
+    const float4 c0 = ld_cg4(src + (g.rc));
+    const float4 c1 = ld_cg4(src + (1u * ps + g.rc));
+    const float4 c3 = ld_cg4(src + (3u * ps + g.rc));
+    const float4 s2 = ld_cg4(src + (2u * ps + g.rs));
+    const float4 s5 = ld_cg4(src + (5u * ps + g.rs));
+    const float4 s6 = ld_cg4(src + (6u * ps + g.rs));
+    const float4 n4 = ld_cg4(src + (4u * ps + g.rn));
+    const float4 n7 = ld_cg4(src + (7u * ps + g.rn));
+    const float4 n8 = ld_cg4(src + (8u * ps + g.rn));
     // ---- the elements that cross the warp's x range (one lane each side)
     float w1 = 0.f, w5 = 0.f, w8 = 0.f, e3 = 0.f, e6 = 0.f, e7 = 0.f;
     if (g.need_w) {
-        w1 = ld_cg1(src + 1 * ps + rc + g.xw);
-        w5 = ld_cg1(src + 5 * ps + rs + g.xw);
-        w8 = ld_cg1(src + 8 * ps + rn + g.xw);
+        w1 = ld_cg1(src + (1u * ps + g.wc));
+        w5 = ld_cg1(src + (5u * ps + g.ws));
+        w8 = ld_cg1(src + (8u * ps + g.wn));
     }
     if (g.need_e) {
-        e3 = ld_cg1(src + 3 * ps + rc + g.xe);
-        e6 = ld_cg1(src + 6 * ps + rs + g.xe);
-        e7 = ld_cg1(src + 7 * ps + rn + g.xe);
+        e3 = ld_cg1(src + (3u * ps + g.ec));
+        e6 = ld_cg1(src + (6u * ps + g.es));
+        e7 = ld_cg1(src + (7u * ps + g.en));
     }
-    const unsigned mbyte = __ldg(d.mask + (long long)g.h * d.mask_pitch + (g.xc >> 3));
+    const unsigned mbyte = __ldg(d.mask + ((unsigned)(g.lr + 1) * (unsigned)d.mask_pitch + ((unsigned)g.xc >> 3)));
     const unsigned nib = (mbyte >> (g.xc & 4)) & 0xFu;
 
     // ---- lane-crossing elements by shuffle
@@ -91,9 +97,7 @@ __device__ __forceinline__ float process_task(const SlabDev& d, int par, int tas
     p[0][7] = n7.y; p[1][7] = n7.z; p[2][7] = n7.w; p[3][7] = e7;
     p[0][8] = w8;   p[1][8] = n8.x; p[2][8] = n8.y; p[3][8] = n8.z;
 
-    float usum = 0.f;
-#pragma unroll
-    for (int j = 0; j < 4; ++j) usum += collide_cell<S>(p[j], (nib >> j) & 1u, d.omega);
+    float usum = collide4<S>(p, nib, d.omega);
 
     // ---- accelerate_flow for the next step, applied to what this step stores in row ny-2
     if (epilogue_accel && g.lr == d.accel_lr) {
@@ -106,7 +110,7 @@ __device__ __forceinline__ float process_task(const SlabDev& d, int par, int tas
 #pragma unroll
         for (int k = 0; k < 9; ++k) o[k] = make_float4(p[0][k], p[1][k], p[2][k], p[3][k]);
 #pragma unroll
-        for (int k = 0; k < 9; ++k) st_cg4(dst + k * ps + rc + g.x0, o[k]);
+        for (int k = 0; k < 9; ++k) st_cg4(dst + ((unsigned)k * ps + g.rc), o[k]);
         if (!d.wrap_y) {
             // halo push over NVLink: only the three populations that cross the slab edge
             if (g.lr == d.rows - 1) {          // my top row -> up neighbour's bottom halo (row 0)
@@ -127,13 +131,13 @@ __device__ __forceinline__ float process_task(const SlabDev& d, int par, int tas
 // accelerate_flow (d2q9-bgk.c:235-266) applied IN PLACE to one task of row ny-2 of buffer `par`,
 // with the halo push of the touched populations.  Used once per lbm_run, before its first step;
 // later steps get the body force through process_task's epilogue.
-__device__ __forceinline__ void accelerate_task(const SlabDev& d, int par, int task, int lane)
+__device__ __forceinline__ void accelerate_task(const SlabDev& d, int par, int2 td, int lane)
 {
-    const TaskGeom g = task_geom(d, task, lane);
+    const TaskGeom g = task_geom(d, td, lane);
     if (!g.active) return;
     float* b = d.buf[par];
-    const long long off = (long long)g.h * d.nx + g.x0;
-    const unsigned mbyte = __ldg(d.mask + (long long)g.h * d.mask_pitch + (g.x0 >> 3));
+    const long long off = (long long)g.rc;
+    const unsigned mbyte = __ldg(d.mask + ((unsigned)(g.lr + 1) * (unsigned)d.mask_pitch + ((unsigned)g.x0 >> 3)));
     const unsigned nib = (mbyte >> (g.x0 & 4)) & 0xFu;
     const int ks[6] = {1, 3, 5, 6, 7, 8};
     float4 v[9];
@@ -185,7 +189,7 @@ __global__ void __launch_bounds__(256) lbm_step_kernel(SlabDev d, int par, const
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
     const int task = blockIdx.x * nw + warp;
     double s = 0.0;
-    if (task < d.rows * d.tpr) s = (double)process_task<S>(d, par, task, lane, epilogue_accel != 0);
+    if (task < d.rows * d.tpr) s = (double)process_task<S>(d, par, __ldg(d.task_order + task), lane, epilogue_accel != 0);
     s = warp_sum(s);
     if (lane == 0) red[warp] = s;
     __syncthreads();
@@ -201,7 +205,7 @@ __global__ void lbm_accel_kernel(SlabDev d, int par)
     const int lane = threadIdx.x & 31;
     const int chunk = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (d.accel_lr < 0 || chunk >= d.tpr) return;
-    accelerate_task(d, par, d.accel_lr * d.tpr + chunk, lane);
+    accelerate_task(d, par, make_int2(d.accel_lr, chunk), lane);
 }
 
 __global__ void lbm_advance_step_kernel(int* step_ptr, int n) { *step_ptr += n; }
@@ -252,8 +256,8 @@ __global__ void __launch_bounds__(512, 1) lbm_persistent_kernel(SlabDev d, int p
     // ---- prologue: accelerate_flow for the first step of this run, in place
     if (d.accel_lr >= 0) {
         for (int k = warp; k < n_tasks; k += nw) {
-            const int task = __ldg(d.task_order + t_lo + k);
-            if (task / d.tpr == d.accel_lr) accelerate_task(d, par0, task, lane);
+            const int2 td = __ldg(d.task_order + t_lo + k);
+            if (td.x == d.accel_lr) accelerate_task(d, par0, td, lane);
         }
     }
     __syncthreads();
@@ -278,8 +282,8 @@ __global__ void __launch_bounds__(512, 1) lbm_persistent_kernel(SlabDev d, int p
                 wait_deps(d, dep_lo, dep_hi, target, lane);
                 waited = true;
             }
-            const int task = __ldg(d.task_order + t_lo + k);
-            acc += (double)process_task<S>(d, par, task, lane, epi);
+            const int2 td = __ldg(d.task_order + t_lo + k);
+            acc += (double)process_task<S>(d, par, td, lane, epi);
         }
         acc = warp_sum(acc);
         if (lane == 0) red[s & 1][warp] = acc;

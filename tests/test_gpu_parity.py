@@ -129,3 +129,86 @@ def test_errors_are_reported(lbm):
             lat.run(1)          # exceeds max_iters
     with pytest.raises(lbm.LbmError):
         lbm.Lattice(130, 16, 1, 0.1, 0.005, 1.85, np.zeros((16, 130), np.int32))   # nx % 4 != 0
+
+
+def test_cli_end_to_end_judged_by_checker(lbm, golden, tmp_path):
+    """./d2q9-bgk <params> <obstacles> in a scratch directory: stdout in the reference's format
+    (d2q9-bgk.c:220-225), av_vels.dat / final_state.dat judged by the checker (the reference's own
+    check/check.py where its tree exists, else tools/check.py) against the shipped known answers."""
+    import os, re, subprocess, sys
+    import oracle_lib
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = os.path.join(root, "d2q9-bgk")
+    pfile, ofile = oracle_lib.grid_files("128x128")
+    r = subprocess.run([exe, pfile, ofile], cwd=tmp_path, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    lines = r.stdout.splitlines()
+    assert lines[0] == "==done=="
+    assert re.fullmatch(r"Reynolds number:\t\t\d\.\d{12}E[+-]\d\d", lines[1])
+    for i, name in enumerate(("Init", "Compute", "Collate", "Total")):
+        assert re.fullmatch(rf"Elapsed {name} time:\t\t\t\d+\.\d{{6}} \(s\)", lines[2 + i]), lines[2 + i]
+    full, shipped = golden("ref_full_128x128"), golden("shipped_128x128")
+    assert lines[1].split("\t\t")[1] == str(full["reynolds"])           # digit for digit
+    # byte-identical files to the unmodified reference's
+    fs = oracle_lib.format_final_state(full["ux"], full["uy"], full["u"], full["pressure"], full["obstacles"])
+    assert (tmp_path / "final_state.dat").read_text() == fs
+    # the checker against the reference's shipped known answers
+    z = np.zeros_like(shipped["pressure"], dtype=np.float32)
+    (tmp_path / "ref_fs.dat").write_text(oracle_lib.format_final_state(z, z, z, shipped["pressure"], full["obstacles"]))
+    (tmp_path / "ref_av.dat").write_text(oracle_lib.format_av_vels(shipped["av_vels"]))
+    checker = "/root/reference/check/check.py"
+    if not os.path.exists(checker):
+        checker = os.path.join(root, "tools", "check.py")
+    c = subprocess.run([sys.executable, checker, "--ref-av-vels-file", str(tmp_path / "ref_av.dat"),
+                        "--ref-final-state-file", str(tmp_path / "ref_fs.dat"), "--av-vels-file", str(tmp_path / "av_vels.dat"),
+                        "--final-state-file", str(tmp_path / "final_state.dat")], capture_output=True, text=True)
+    assert c.returncode == 0 and "Both tests passed!" in c.stdout, c.stdout
+
+
+@pytest.mark.parametrize("seed", [1, 2026, 99991])
+def test_exact_division_and_sqrt_fast_paths(lbm, seed):
+    """The shared-reciprocal division and the rsqrt-based root used inside the kernel are bit-identical
+    to __fdiv_rn / __fsqrt_rn on 2 x 2^28 hashed operand pairs (incl. zeros and both range limits)."""
+    assert lbm.selftest_math(1 << 28, seed) == 0
+
+
+def _ngpu(lbm):
+    return lbm.device_count()
+
+
+@pytest.mark.parametrize("ngpus", [2, 3, 4, 8])
+@pytest.mark.parametrize("grid,steps", [("128x256", 400), ("1024x1024", 150), ("128x128", 301)])
+def test_row_slabs_over_nvlink_equal_single_gpu(lbm, ngpus, grid, steps):
+    """Row decomposition over N GPUs (reference: allocate_rows + halo_exchange, d2q9-bgk.c:341-393,
+    483-503), halos pushed over NVLink from inside the kernel: the lattice must equal the single-GPU
+    lattice bit for bit (128x256 has periodic top/bottom, i.e. exercises the ring wrap link), and
+    av_vels must agree to the rounding of the final double->float conversion."""
+    if _ngpu(lbm) < ngpus:
+        pytest.skip(f"needs {ngpus} GPUs")
+    p, mask, lines = load_grid(grid)
+    with make(lbm, p, mask, lines, iters=steps) as one:
+        one.run(steps)
+        f1, av1 = one.cells(), one.av_vels()
+    with make(lbm, p, mask, lines, iters=steps, ngpus=ngpus) as many:
+        assert many.num_slabs() == ngpus
+        many.run(steps // 3)
+        many.run(steps - steps // 3)       # a second launch re-arms the neighbour flags
+        fn, avn = many.cells(), many.av_vels()
+        pr = many.final_state()[3]
+    assert np.array_equal(f1, fn)
+    np.testing.assert_allclose(avn, av1, rtol=3e-7)
+    assert np.all(np.isfinite(pr))
+
+
+def test_two_gpu_random_state_matches_oracle(lbm, oracle):
+    if _ngpu(lbm) < 2:
+        pytest.skip("needs 2 GPUs")
+    nx, ny = 256, 37
+    mask, f0 = random_case(nx, ny, seed=7, walls=False)
+    p = dict(nx=nx, ny=ny, density=0.1, accel=0.005, omega=1.85)
+    ref_f, ref_tot = oracle.run(nx, ny, 9, p["density"], p["accel"], p["omega"], mask, f=f0)
+    with make(lbm, p, mask, iters=9, ngpus=2) as lat:
+        lat.set_cells(f0)
+        lat.run(9)
+        got = lat.cells()
+    assert np.array_equal(got, ref_f)
