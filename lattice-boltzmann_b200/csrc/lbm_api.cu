@@ -403,9 +403,10 @@ void describe(lbm_ctx* c)
 {
     const Slab& s = c->slabs[0];
     snprintf(c->desc, sizeof(c->desc),
-             "engine=%s fp=%s slabs=%d/%d ctas/slab=%d threads/cta=%d tasks/slab=%d tasks/row=%d",
+             "engine=%s fp=%s slabs=%d/%d ctas/slab=%d threads/cta=%d tasks/slab=%d tasks/row=%d strips=%d interior=%.0f%%",
              c->engine == 1 ? "persistent-neighbour-sync" : "launch-per-step-graph", c->strict ? "strict" : "fast",
-             c->nslabs, c->size, s.plan.num_ctas, c->threads, s.plan.num_tasks, s.plan.tpr);
+             c->nslabs, c->size, s.plan.num_ctas, c->threads, s.plan.num_tasks, s.plan.tpr, s.plan.strips,
+             100.0 * lbm::interior_fraction(s.plan));
 }
 
 }  // namespace
@@ -448,8 +449,12 @@ int lbm_plan_selftest(int nx, int ny, int size, int ctas)
             const lbm::SlabPlan& dn = plans[(r - 1 + size) % size];
             if (p.ctas_up != up.num_ctas || p.ctas_down != dn.num_ctas) return fail("rank %d: neighbour CTA counts disagree", r);
             for (int b = 0; b < p.num_ctas; ++b) {
-                const bool owns_first = lbm::range_begin(p.num_tasks, p.num_ctas, b) < p.tpr;
-                const bool owns_last = lbm::range_begin(p.num_tasks, p.num_ctas, b + 1) > (int64_t)(p.rows - 1) * p.tpr;
+                const lbm::Layout L = lbm::make_layout(p.tpr, p.rows, p.num_ctas);
+                bool owns_first = false, owns_last = false;
+                for (int ch = 0; ch < p.tpr; ++ch) {
+                    owns_first = owns_first || L.owner(0, ch) == b;
+                    owns_last = owns_last || L.owner(p.rows - 1, ch) == b;
+                }
                 if ((p.pub_down[b] >= 0) != owns_first || (p.pub_up[b] >= 0) != owns_last)
                     return fail("rank %d cta %d: publish flags do not match row ownership", r, b);
                 if (owns_first) {   // I am in dn's up_owners section

@@ -2,6 +2,7 @@
 #include "lbm_plan.hpp"
 
 #include <algorithm>
+#include <cstdlib>
 #include <set>
 #include <sstream>
 #include <stdexcept>
@@ -35,17 +36,74 @@ int choose_ctas(int nx, int rows, int max_resident)
     return (int)std::max<int64_t>(g, 1);
 }
 
+int Layout::strip_of(int ch) const
+{
+    int s = (int)((int64_t)ch * strips / tpr);
+    while (s + 1 < strips && c0[s + 1] <= ch) ++s;
+    while (s > 0 && c0[s] > ch) --s;
+    return s;
+}
+
+int64_t Layout::pos(int lr, int ch) const
+{
+    const int s = strip_of(ch);
+    const int w = c0[s + 1] - c0[s];
+    return (int64_t)rows * c0[s] + (int64_t)lr * w + (ch - c0[s]);
+}
+
+void Layout::task_at(int64_t p, int* lr, int* ch) const
+{
+    int s = (int)(p / ((int64_t)rows * tpr / strips + 1));
+    if (s >= strips) s = strips - 1;
+    while (s + 1 < strips && (int64_t)rows * c0[s + 1] <= p) ++s;
+    while (s > 0 && (int64_t)rows * c0[s] > p) --s;
+    const int w = c0[s + 1] - c0[s];
+    const int64_t q = p - (int64_t)rows * c0[s];
+    *lr = (int)(q / w);
+    *ch = c0[s] + (int)(q % w);
+}
+
+int Layout::owner(int lr, int ch) const { return owner_of(tasks(), ctas, pos(lr, ch)); }
+
+Layout make_layout(int tpr, int rows, int ctas)
+{
+    // A CTA's patch is ~n/w rows of a strip w chunks wide; its interior is what is not on the rim (a
+    // full-width strip has no left/right rim: x is periodic inside the CTA's own rows).  Measured on
+    // B200 (profiles/r01_sweep.md): wide strips stream best from HBM, but a patch with no interior
+    // (e.g. 16384x128 per GPU at 8 GPUs: half a row per CTA) loses 13 % to flag latency.  So: the FEWEST
+    // strips whose expected interior share reaches 30 %, else the count with the largest share.
+    Layout best;
+    double best_score = -1.0;
+    const double n = (double)tpr * rows / ctas;     // tasks per CTA
+    for (int strips = 1; strips <= tpr; ++strips) {
+        const double w = (double)tpr / strips;
+        if (strips > 1 && w < 3.0) break;
+        const double h = n / w;
+        const double score = std::max(0.0, h - 2.0) * (strips == 1 ? w : std::max(0.0, w - 2.0)) / n;
+        if (score > best_score) {
+            best_score = score;
+            best.strips = strips;
+        }
+        if (score >= 0.30) break;
+    }
+    if (const char* e = getenv("LBM_STRIPS")) {       // tuning override
+        const int v = atoi(e);
+        if (v >= 1 && v <= tpr) best.strips = v;
+    }
+    best.tpr = tpr; best.rows = rows; best.ctas = ctas;
+    best.c0.resize(best.strips + 1);
+    for (int s = 0; s <= best.strips; ++s) best.c0[s] = (int)((int64_t)tpr * s / best.strips);
+    return best;
+}
+
 namespace {
 
 // CTAs (ascending) that own at least one task of local row `lr` of a slab.
-std::vector<int> row_owners(int tpr, int rows, int ctas, int lr)
+std::vector<int> row_owners(const Layout& L, int lr)
 {
-    const int64_t tasks = (int64_t)tpr * rows;
-    const int first = owner_of(tasks, ctas, (int64_t)lr * tpr);
-    const int last = owner_of(tasks, ctas, (int64_t)lr * tpr + tpr - 1);
-    std::vector<int> v;
-    for (int b = first; b <= last; ++b) v.push_back(b);
-    return v;
+    std::set<int> o;
+    for (int ch = 0; ch < L.tpr; ++ch) o.insert(L.owner(lr, ch));
+    return std::vector<int>(o.begin(), o.end());
 }
 
 int index_in(const std::vector<int>& v, int x)
@@ -82,9 +140,14 @@ SlabPlan make_plan(int nx, int ny, int rank, int size, int ctas, int ctas_up, in
 
     const int G = ctas;
     const int64_t T = p.num_tasks;
+    const Layout L = make_layout(p.tpr, p.rows, G);
+    p.strips = L.strips;
+    Layout Lup, Ldn;
     if (!single) {
-        p.up_owners = row_owners(p.tpr, p.rows_up, p.ctas_up, 0);
-        p.down_owners = row_owners(p.tpr, p.rows_down, p.ctas_down, p.rows_down - 1);
+        Lup = make_layout(p.tpr, p.rows_up, p.ctas_up);
+        Ldn = make_layout(p.tpr, p.rows_down, p.ctas_down);
+        p.up_owners = row_owners(Lup, 0);
+        p.down_owners = row_owners(Ldn, p.rows_down - 1);
     }
     p.num_flags = G + (int)p.up_owners.size() + (int)p.down_owners.size();
     const int up_base = G, down_base = G + (int)p.up_owners.size();
@@ -96,12 +159,26 @@ SlabPlan make_plan(int nx, int ny, int rank, int size, int ctas, int ctas_up, in
     p.pub_up.assign(G, -1);
     p.pub_down.assign(G, -1);
 
+    std::vector<int> first_owners, last_owners;
+    int n_up_section = 0;
+    if (!single) {
+        first_owners = row_owners(L, 0);
+        last_owners = row_owners(L, p.rows - 1);
+        // The UP neighbour's flag array is [its G | its up_owners | its down_owners]; its up_owners are the
+        // first-row owners of ITS up neighbour.  All slabs are assumed to run the same CTA budget.
+        const int upup = (up + 1) % size;
+        const int rows_upup = allocate_rows(ny, size, upup).rows;
+        const int ctas_upup = std::min((upup == rank) ? G : ctas_up, p.tpr * rows_upup);
+        n_up_section = (int)row_owners(make_layout(p.tpr, rows_upup, ctas_upup), 0).size();
+    }
+
     for (int b = 0; b < G; ++b) {
         const int64_t lo = range_begin(T, G, b), hi = range_begin(T, G, b + 1);
         std::vector<int> interior, boundary;
         std::set<int> dep;
-        for (int64_t t = lo; t < hi; ++t) {
-            const int lr = (int)(t / p.tpr), ch = (int)(t % p.tpr);
+        for (int64_t q = lo; q < hi; ++q) {
+            int lr, ch;
+            L.task_at(q, &lr, &ch);
             bool inside = true;
             for (int dy = -1; dy <= 1; ++dy) {
                 for (int dx = -1; dx <= 1; ++dx) {
@@ -113,22 +190,16 @@ SlabPlan make_plan(int nx, int ny, int rank, int size, int ctas, int ctas_up, in
                         } else {
                             // remote row: last real row of `down` (dy<0) or first real row of `up`
                             inside = false;
-                            if (r2 < 0) {
-                                const int o = owner_of((int64_t)p.tpr * p.rows_down, p.ctas_down,
-                                                       (int64_t)(p.rows_down - 1) * p.tpr + c2);
-                                dep.insert(down_base + index_in(p.down_owners, o));
-                            } else {
-                                const int o = owner_of((int64_t)p.tpr * p.rows_up, p.ctas_up, c2);
-                                dep.insert(up_base + index_in(p.up_owners, o));
-                            }
+                            if (r2 < 0) dep.insert(down_base + index_in(p.down_owners, Ldn.owner(p.rows_down - 1, c2)));
+                            else dep.insert(up_base + index_in(p.up_owners, Lup.owner(0, c2)));
                             continue;
                         }
                     }
-                    const int o = owner_of(T, G, (int64_t)r2 * p.tpr + c2);
+                    const int o = L.owner(r2, c2);
                     if (o != b) { inside = false; dep.insert(o); }
                 }
             }
-            (inside ? interior : boundary).push_back((int)t);
+            (inside ? interior : boundary).push_back(lr * p.tpr + ch);
         }
         p.n_interior[b] = (int)interior.size();
         p.task_order.insert(p.task_order.end(), interior.begin(), interior.end());
@@ -138,25 +209,11 @@ SlabPlan make_plan(int nx, int ny, int rank, int size, int ctas, int ctas_up, in
         p.dep_begin[b + 1] = (int)p.deps.size();
 
         if (!single) {
-            // I mirror my progress to the DOWN neighbour if I own part of my first real row:
-            // there I appear in its up_owners list (its up neighbour is me).
-            const int64_t row0_end = p.tpr;                       // tasks [0, tpr)
-            const int64_t rowL_begin = (int64_t)(p.rows - 1) * p.tpr;
-            if (lo < row0_end) {
-                const std::vector<int> mine = row_owners(p.tpr, p.rows, G, 0);
-                p.pub_down[b] = p.ctas_down + index_in(mine, b);
-            }
-            if (hi > rowL_begin) {
-                // in the UP neighbour's flag array: after its G and its up_owners section.
-                // Its up_owners section length = owners of the first real row of ITS up neighbour.
-                const int upup = (up + 1) % size;
-                const int rows_upup = allocate_rows(ny, size, upup).rows;
-                // all slabs are assumed to use the same CTA budget as passed for `up`
-                const int ctas_upup = std::min((upup == rank) ? G : ctas_up, p.tpr * rows_upup);
-                const int n_up_section = (int)row_owners(p.tpr, rows_upup, ctas_upup, 0).size();
-                const std::vector<int> mine = row_owners(p.tpr, p.rows, G, p.rows - 1);
-                p.pub_up[b] = p.ctas_up + n_up_section + index_in(mine, b);
-            }
+            // I mirror my progress to the DOWN neighbour if I own part of my first real row (there I am in
+            // its up_owners section), and to the UP neighbour if I own part of my last real row.
+            const int i0 = index_in(first_owners, b), i1 = index_in(last_owners, b);
+            if (i0 >= 0) p.pub_down[b] = p.ctas_down + i0;
+            if (i1 >= 0) p.pub_up[b] = p.ctas_up + n_up_section + i1;
         }
     }
     return p;
@@ -164,9 +221,9 @@ SlabPlan make_plan(int nx, int ny, int rank, int size, int ctas, int ctas_up, in
 
 std::string validate_plan(const SlabPlan& p)
 {
-    std::ostringstream err;
     const int G = p.num_ctas;
     const int64_t T = p.num_tasks;
+    const Layout L = make_layout(p.tpr, p.rows, G);
     std::vector<int> seen(T, 0);
     if ((int)p.task_order.size() != T) return "task_order size";
     for (int b = 0; b < G; ++b) {
@@ -175,30 +232,42 @@ std::string validate_plan(const SlabPlan& p)
         std::set<int> dep(p.deps.begin() + p.dep_begin[b], p.deps.begin() + p.dep_begin[b + 1]);
         for (int k = p.task_begin[b]; k < p.task_begin[b + 1]; ++k) {
             const int t = p.task_order[k];
-            if (t < lo || t >= hi) return "task outside owner range";
+            if (t < 0 || t >= T) return "task id out of range";
+            const int lr = t / p.tpr, ch = t % p.tpr;
+            if (L.owner(lr, ch) != b) return "task outside owner range";
             if (seen[t]++) return "task listed twice";
             const bool is_int = (k - p.task_begin[b]) < p.n_interior[b];
-            const int lr = t / p.tpr, ch = t % p.tpr;
+            bool all_mine = true;
             for (int dy = -1; dy <= 1; ++dy)
                 for (int dx = -1; dx <= 1; ++dx) {
                     const int c2 = (ch + dx + p.tpr) % p.tpr;
                     int r2 = lr + dy;
                     if (r2 < 0 || r2 >= p.rows) {
                         if (p.size == 1) r2 = (r2 + p.rows) % p.rows;
-                        else { if (is_int) return "interior task touches a remote row"; continue; }
+                        else { all_mine = false; if (is_int) return "interior task touches a remote row"; continue; }
                     }
-                    const int o = owner_of(T, G, (int64_t)r2 * p.tpr + c2);
+                    const int o = L.owner(r2, c2);
                     if (o != b) {
+                        all_mine = false;
                         if (is_int) return "interior task with foreign neighbour";
                         if (!dep.count(o)) return "missing dependency";
                     }
                 }
+            if (all_mine && !is_int) return "self-contained task scheduled as boundary";
         }
         for (int d : dep) if (d < 0 || d >= p.num_flags || d == b) return "bad dependency index";
     }
     for (int64_t t = 0; t < T; ++t) if (seen[t] != 1) return "task missing";
     if (p.num_flags != G + (int)p.up_owners.size() + (int)p.down_owners.size()) return "num_flags";
     return "";
+}
+
+// Fraction of tasks that are interior (diagnostic for tests / describe()).
+double interior_fraction(const SlabPlan& p)
+{
+    long long n = 0;
+    for (int v : p.n_interior) n += v;
+    return p.num_tasks ? (double)n / p.num_tasks : 0.0;
 }
 
 }  // namespace lbm

@@ -38,8 +38,25 @@ SlabShape allocate_rows(int ny, int size, int rank);
 // Even contiguous split of `tasks` over `ctas`: CTA b owns [begin(b), begin(b+1)).
 inline int64_t range_begin(int64_t tasks, int ctas, int b) { return tasks * b / ctas; }
 
+// Ownership layout of one slab: the rows x tpr grid of tasks is cut into vertical STRIPS of about
+// `strip_w` chunks; tasks are ordered strip by strip, row-major inside a strip, and that sequence is cut
+// into `ctas` equal ranges.  Every CTA therefore owns a compact patch (a few rows of one strip) with a
+// perfectly balanced task count, and most of its tasks are interior.  strip_w == tpr is plain row-major.
+struct Layout {
+    int tpr = 0, rows = 0, ctas = 0, strips = 1;
+    std::vector<int> c0;    // first chunk of strip s (size strips+1)
+    int64_t tasks() const { return (int64_t)tpr * rows; }
+    int strip_of(int ch) const;
+    int64_t pos(int lr, int ch) const;        // position in the strip-major sequence
+    void task_at(int64_t pos, int* lr, int* ch) const;
+    int owner(int lr, int ch) const;
+};
+// Picks the strip count that maximises the expected number of interior tasks per CTA.
+Layout make_layout(int tpr, int rows, int ctas);
+
 struct SlabPlan {
     int nx = 0, rows = 0, row_start = 0;
+    int strips = 1;
     int rank = 0, size = 1;
     int tpr = 0;          // tasks per row
     int num_tasks = 0;
@@ -76,5 +93,6 @@ int choose_ctas(int nx, int rows, int max_resident);
 // all neighbours inside the CTA, every neighbour owner of a boundary task is in deps, mirror
 // indices are consistent between neighbouring plans.  Returns "" or a description.
 std::string validate_plan(const SlabPlan& p);
+double interior_fraction(const SlabPlan& p);
 
 }  // namespace lbm

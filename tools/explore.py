@@ -16,12 +16,24 @@ def main():
     ap.add_argument("--steps", type=int, default=2000)
     ap.add_argument("--reps", type=int, default=3)
     ap.add_argument("--ngpus", type=int, default=1)
+    ap.add_argument("--synthetic", default=None, help="NXxNY: closed box + walls at nx/4, nx/2 instead of a shipped grid")
     ap.add_argument("--configs", default="1:256:2:1,1:512:1:1,1:256:1:1,1:128:4:1,1:256:2:2,2:256:0:1")
     args = ap.parse_args()
     pfile = os.path.join(ROOT, "inputs", f"input_{args.grid}.params")
     ofile = os.path.join(ROOT, "inputs", f"obstacles_{args.grid}.dat")
-    p = lbm.read_params(pfile)
-    mask, lines = lbm.read_obstacles(ofile, p["nx"], p["ny"])
+    if args.synthetic:
+        import numpy as np
+        nx, ny = (int(v) for v in args.synthetic.split("x"))
+        p = dict(nx=nx, ny=ny, density=0.1, accel=0.01, omega=1.85)
+        mask = np.zeros((ny, nx), np.int32)
+        mask[0, :] = mask[-1, :] = 1
+        mask[:, 0] = mask[:, -1] = 1
+        mask[:, nx // 4] = mask[:, nx // 2] = 1
+        lines = int(mask.sum())
+        args.grid = args.synthetic
+    else:
+        p = lbm.read_params(pfile)
+        mask, lines = lbm.read_obstacles(ofile, p["nx"], p["ny"])
     cells = p["nx"] * p["ny"]
     for cfg in args.configs.split(","):
         engine, threads, cps, fp = (int(v) for v in cfg.split(":"))
