@@ -6,10 +6,12 @@
 
 A "step" is one complete run of the workload's time loop (maxIters timesteps of
 accelerate_flow + propagate + rebound + collision + av_velocity) from device-resident state.
-  N = 1 : workload 1024x1024 (BASELINE.json's single-GPU roofline headline); the JSON line
-          also carries the single-GPU figure of the strong-scaling workload under "also".
-  N > 1 : workload 16384x1024 row-decomposed over the N GPUs (strong scaling), three-population
-          one-row halos pushed over NVLink peer memory from inside the kernel.
+Workload at every N: 16384x1024 (BASELINE.json's 1/2/4/8-GPU strong-scaling configuration; 1.2 GB
+A/B working set, i.e. the honest HBM-bound case), row-decomposed over the N GPUs with
+three-population one-row halos pushed over NVLink peer memory from inside the kernel.  One
+workload for all N keeps the driver's scaling efficiency meaningful.  At N = 1 the line also
+carries BASELINE.json's single-GPU roofline headline, 1024x1024, under "also" (75 MB A/B set:
+L2-resident inside a step, so it can exceed the HBM roofline).
 value   = lattice updates of all ranks / device time (CUDA events on the launching stream, max
           over ranks), in GLUPS.
 e2e     = the same metric through the public C ABI with HOST buffers: lbm_create (mask +
@@ -44,6 +46,17 @@ def hbm_peak():
             return float(json.load(fh)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
     except Exception:
         return FALLBACK_HBM_GBS, "fallback (B200_PROFILING.md)"
+
+
+def measured_traffic(grid, updates_per_launch):
+    """DRAM bytes of one timestep-kernel launch, from the committed ncu capture (bytes per cell update
+    measured on a shorter launch of the same kernel and grid, scaled to this launch's update count)."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as fh:
+            per = json.load(fh)["dram_bytes_per_cell_update"][grid]
+        return per * updates_per_launch
+    except Exception:
+        return None
 
 
 def grid_files(grid):
@@ -137,7 +150,7 @@ def reference_arm(args, rank, world):
     """bench.py --impl reference: the reference's own CPU implementation on this box's host cores."""
     if rank != 0:
         return 0
-    grid = args.workload or ("1024x1024" if args.gpus == 1 else "16384x1024")
+    grid = args.workload or "16384x1024"
     threads = host_cores()
     try:
         iters = reference_sample_iters(grid, threads, args.ref_seconds)
@@ -309,17 +322,21 @@ def main():
         raise SystemExit(f"bench.py: --gpus {args.gpus} needs {args.gpus} ranks (torchrun), got WORLD_SIZE={world}")
     scratch = torch.zeros(64 * 1024 * 1024, dtype=torch.float32, device="cuda")
 
-    grid = args.workload or ("1024x1024" if world == 1 else "16384x1024")
+    grid = args.workload or "16384x1024"
     iters = args.iters or lbm.read_params(grid_files(grid)[0])["max_iters"]
     res = time_resident(lbm, torch, grid, iters, args.steps, args.warmup, rank, world, dist, scratch)
     e2e = time_e2e(lbm, torch, grid, iters, max(1, min(args.steps, 3)), rank, world, dist)
     also = None
     if world == 1 and not args.workload:
-        big = "16384x1024"
-        r2 = time_resident(lbm, torch, big, 1000, 3, 3, rank, world, dist, scratch)
-        also = {big: {"value": r2["glups"], "unit": "GLUPS", "iters_per_step": 1000, "steps": 3,
-                      "roofline_frac": r2["glups"] * BYTES_PER_UPDATE / hbm_peak()[0],
-                      "note": "single-GPU figure of the strong-scaling workload; 1.2 GB working set, HBM-bound"}}
+        head = "1024x1024"
+        hi = lbm.read_params(grid_files(head)[0])["max_iters"]
+        r2 = time_resident(lbm, torch, head, hi, max(3, args.steps), 3, rank, world, dist, scratch)
+        e2 = time_e2e(lbm, torch, head, hi, 3, rank, world, dist)
+        also = {head: {"value": r2["glups"], "unit": "GLUPS", "iters_per_step": hi, "steps": max(3, args.steps),
+                       "ms_per_step": r2["ms_per_step"], "roofline_frac": r2["glups"] * BYTES_PER_UPDATE / hbm_peak()[0],
+                       "e2e": e2["glups"], "gpu_launches": r2["launches"],
+                       "note": "BASELINE.json's single-GPU roofline headline; 75 MB A/B set is L2-resident inside a step, "
+                               "so the algorithmic rate may exceed the HBM roofline (ncu: 21 B of DRAM traffic per update)"}}
     if rank == 0:
         peak, how = hbm_peak()
         achieved = res["glups"] * BYTES_PER_UPDATE / world      # GB/s per GPU
@@ -329,12 +346,14 @@ def main():
                 "config": {"workload": grid, "nx": res["nx"], "ny": res["ny"], "iters_per_step": iters,
                            "parallelism": f"row-slabs x{world}" if world > 1 else "single GPU",
                            "engine": res["desc"],
-                           "l2": "256 MiB flush between steps; within a step the time loop re-reads its own output"
-                                 " (1024x1024: 75 MB A/B set stays L2-resident by nature; 16384x1024: 1.2 GB, HBM-bound)",
+                           "l2": "working set 1.2 GB >> 126 MB L2 (inputs larger than L2); additionally a 256 MiB flush between steps",
                            "inputs": "shipped-format params/obstacles regenerated by tools/gen_inputs.py (no RNG)"},
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                             "traffic": None, "peak_source": how,
-                             "note": "achieved = 72 B x cell updates / CUDA-event time of the timestep kernel, per GPU"},
+                             "traffic": measured_traffic(grid, float(res["nx"]) * res["ny"] * iters / world),
+                             "algorithmic_bytes_per_launch": BYTES_PER_UPDATE * res["nx"] * res["ny"] * iters / world,
+                             "peak_source": how,
+                             "note": "achieved = 72 B x cell updates of one persistent launch / its CUDA-event time, per GPU; "
+                                     "traffic = ncu dram bytes per cell update (profiles/traffic.json) x updates per launch per GPU"},
                 "e2e": {"value": e2e["glups"], "unit": "GLUPS", "h2d_bytes_per_step": e2e["h2d"], "d2h_bytes_per_step": e2e["d2h"],
                         "note": "lbm_create + lbm_run + lbm_get_av_vels + lbm_get_cells + lbm_destroy per step, host buffers"},
                 "gpu_launches": res["launches"], "clocks": res["clocks"], "wall_s_timed_region": res["wall_s"]}

@@ -2,7 +2,7 @@
 # ncu evidence for profiles/: launch list of the bench command + full captures of the timestep kernel.
 set -u
 mkdir -p gpurun_out
-B="python bench.py --steps 1 --warmup 3 --iters 300 --no-cpu-baseline"
+B="python bench.py --steps 1 --warmup 3 --iters 100 --no-cpu-baseline"
 echo "== launch list of: $B"
 $B > gpurun_out/plain_bench.log 2>&1 && ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/launches_bench.csv $B > gpurun_out/ncu_list.log 2>&1
 echo "rc=$?"
