@@ -186,6 +186,7 @@ def flush_l2(torch, scratch):
 
 def time_resident(lbm, torch, grid, iters, steps, warmup, rank, world, dist, scratch):
     """value leg: state resident in HBM, K steps of `iters` timesteps. Returns dict."""
+    ring = importlib.import_module("lattice-boltzmann_b200.ring")
     pfile, ofile = grid_files(grid)
     p = lbm.read_params(pfile)
     mask, lines = lbm.read_obstacles(ofile, p["nx"], p["ny"])
@@ -194,10 +195,8 @@ def time_resident(lbm, torch, grid, iters, steps, warmup, rank, world, dist, scr
     if world > 1:
         lat = lbm.Lattice(p["nx"], p["ny"], cap, p["density"], p["accel"], p["omega"], mask,
                           rank=rank, size=world, device=torch.cuda.current_device(), **common)
-        blob = torch.frombuffer(bytearray(lat.rank_export()), dtype=torch.uint8).cuda()
-        blobs = [torch.empty_like(blob) for _ in range(world)]
-        dist.all_gather(blobs, blob)
-        lat.rank_connect(bytes(blobs[(rank + 1) % world].cpu().numpy()), bytes(blobs[(rank - 1) % world].cpu().numpy()))
+        up, down, _ = ring.exchange_blobs(dist, torch, lat.rank_export(), rank, world, device="cuda")
+        lat.rank_connect(up, down)
     else:
         lat = lbm.Lattice(p["nx"], p["ny"], cap, p["density"], p["accel"], p["omega"], mask, ngpus=1, **common)
     lat.sync()
@@ -246,6 +245,7 @@ def time_resident(lbm, torch, grid, iters, steps, warmup, rank, world, dist, scr
 def time_e2e(lbm, torch, grid, iters, steps, rank, world, dist):
     """e2e leg: host buffers in, host buffers out, through the public API, every step."""
     import numpy as np
+    ring = importlib.import_module("lattice-boltzmann_b200.ring")
     pfile, ofile = grid_files(grid)
     p = lbm.read_params(pfile)
     mask, lines = lbm.read_obstacles(ofile, p["nx"], p["ny"])
@@ -258,19 +258,15 @@ def time_e2e(lbm, torch, grid, iters, steps, rank, world, dist):
         if world > 1:
             lat = lbm.Lattice(p["nx"], p["ny"], iters, p["density"], p["accel"], p["omega"], mask, obstacle_lines=lines,
                               rank=rank, size=world, device=torch.cuda.current_device())
-            blob = torch.frombuffer(bytearray(lat.rank_export()), dtype=torch.uint8).cuda()
-            blobs = [torch.empty_like(blob) for _ in range(world)]
-            dist.all_gather(blobs, blob)
-            lat.rank_connect(bytes(blobs[(rank + 1) % world].cpu().numpy()), bytes(blobs[(rank - 1) % world].cpu().numpy()))
+            up, down, _ = ring.exchange_blobs(dist, torch, lat.rank_export(), rank, world, device="cuda")
+            lat.rank_connect(up, down)
         else:
             lat = lbm.Lattice(p["nx"], p["ny"], iters, p["density"], p["accel"], p["omega"], mask, obstacle_lines=lines)
         lat.run(iters)
         av = lat.av_vels()
         f = lat.cells()
         if world > 1:
-            t = torch.from_numpy(av.astype(np.float64)).cuda()
-            dist.all_reduce(t)               # the one end-of-run sum of per-rank partials (reference :445)
-            av = (t.cpu().numpy() * float(lat.inv_free_cells())).astype(np.float32)
+            av = ring.reduce_av_vels(dist, torch, av, lat.inv_free_cells(), device="cuda")   # reference :445-446
             dist.barrier()                   # neighbours must be done with my halo rows before I free them
         a, b = lat.transfer_bytes()
         h2d += a
