@@ -141,6 +141,13 @@ int lbm_transfer_bytes(const lbm_ctx* ctx, long long* h2d, long long* d2h);
 /* Human-readable description of the engine configuration chosen (static buffer in ctx). */
 const char* lbm_describe(lbm_ctx* ctx);
 
+/* Diagnostics of the persistent engine (off unless the environment has LBM_PROFILE=1 when the
+ * context is created): per CTA and warp, the SM cycles of the most recent lbm_run spent waiting
+ * for neighbouring CTAs (progress flags), waiting at the CTA's end-of-step barrier, pulling
+ * tagged halo slots of a neighbouring GPU (load + spin), and in total.  out receives num_ctas * warps * 4 values ([cta][warp][4]);
+ * out may be NULL to query the sizes. */
+int lbm_get_profile(lbm_ctx* ctx, int slab, long long* out, int capacity, int* num_ctas, int* warps);
+
 /* The reference's row decomposition as a pure function (allocate_rows, :483-503):
  * rows/start of rank r of `size`, and which rank owns global row ny-2.  Host-only. */
 int lbm_allocate_rows(int ny, int size, int rank, int* row_start, int* rows);

@@ -65,6 +65,7 @@ SYMBOLS = {
     "lbm_last_run_launches": (ctypes.c_int, [_P]),
     "lbm_transfer_bytes": (ctypes.c_int, [_P, ctypes.POINTER(ctypes.c_longlong), ctypes.POINTER(ctypes.c_longlong)]),
     "lbm_describe": (ctypes.c_char_p, [_P]),
+    "lbm_get_profile": (ctypes.c_int, [_P, ctypes.c_int, _P, ctypes.c_int, _IP, _IP]),
     "lbm_allocate_rows": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, ctypes.c_int, _IP, _IP]),
     "lbm_plan_selftest": (ctypes.c_int, [ctypes.c_int] * 4),
     "lbm_selftest_math": (ctypes.c_int, [ctypes.c_longlong, ctypes.c_longlong, ctypes.POINTER(ctypes.c_longlong)]),
@@ -253,6 +254,14 @@ class Lattice:
 
     def describe(self):
         return (self.lib.lbm_describe(self._ctx) or b"").decode()
+
+    def profile(self, slab=0):
+        """[cta, warp, (wait, barrier, publish, total)] SM cycles of the last run (needs LBM_PROFILE=1)."""
+        g, w = ctypes.c_int(), ctypes.c_int()
+        self._ck(self.lib.lbm_get_profile(self._ctx, slab, None, 0, ctypes.byref(g), ctypes.byref(w)))
+        out = np.zeros((g.value, w.value, 4), np.int64)
+        self._ck(self.lib.lbm_get_profile(self._ctx, slab, out.ctypes.data, out.size, None, None))
+        return out
 
     def num_slabs(self):
         return self.lib.lbm_num_slabs(self._ctx)

@@ -53,15 +53,15 @@ struct Slab {
     int* step_ptr = nullptr;       // engine 2: device copy of steps_done
     float* fields = nullptr;       // scratch for final-state planes (4 * rows * nx)
     double* scal = nullptr;        // scratch for scalar reductions (2 doubles)
+    long long* prof = nullptr;     // LBM_PROFILE=1: per-warp cycle counters of the persistent engine
     // engine 2
     cudaGraphExec_t graph = nullptr;
     int graph_steps = 0;
     int graph_par = -1;
-    // IPC (one-process-per-GPU mode)
-    void* ipc_up_buf[2] = {nullptr, nullptr};
-    void* ipc_down_buf[2] = {nullptr, nullptr};
-    void* ipc_up_flags = nullptr;
-    void* ipc_down_flags = nullptr;
+    uint2* ll_in = nullptr;        // inbound halo slots [parity 2][side 2][pop 3][nx] (multi-slab only)
+    // IPC (one-process-per-GPU mode): the ring neighbours' inbound halo slots
+    void* ipc_ll_up = nullptr;
+    void* ipc_ll_down = nullptr;
     int finalized_steps = 0;       // partials already folded into tot
 };
 
@@ -255,15 +255,11 @@ void slab_free(Slab& s)
     if (s.stream == nullptr && s.buf[0] == nullptr) return;
     cudaSetDevice(s.device);
     if (s.graph) cudaGraphExecDestroy(s.graph);
-    for (int i = 0; i < 2; ++i) {
-        if (s.ipc_up_buf[i]) cudaIpcCloseMemHandle(s.ipc_up_buf[i]);
-        if (s.ipc_down_buf[i] && s.ipc_down_buf[i] != s.ipc_up_buf[i]) cudaIpcCloseMemHandle(s.ipc_down_buf[i]);
-    }
-    if (s.ipc_up_flags) cudaIpcCloseMemHandle(s.ipc_up_flags);
-    if (s.ipc_down_flags && s.ipc_down_flags != s.ipc_up_flags) cudaIpcCloseMemHandle(s.ipc_down_flags);
+    if (s.ipc_ll_up) cudaIpcCloseMemHandle(s.ipc_ll_up);
+    if (s.ipc_ll_down && s.ipc_ll_down != s.ipc_ll_up) cudaIpcCloseMemHandle(s.ipc_ll_down);
     cudaFree(s.buf[0]); cudaFree(s.buf[1]); cudaFree(s.mask); cudaFree(s.sched); cudaFree(s.flags);
     cudaFree(s.partials); cudaFree(s.tot); cudaFree(s.status); cudaFree(s.step_ptr); cudaFree(s.fields);
-    cudaFree(s.scal);
+    cudaFree(s.scal); cudaFree(s.prof); cudaFree(s.ll_in);
     if (s.ev_start) cudaEventDestroy(s.ev_start);
     if (s.ev_stop) cudaEventDestroy(s.ev_stop);
     if (s.stream) cudaStreamDestroy(s.stream);
@@ -306,7 +302,7 @@ int slab_create(lbm_ctx* c, Slab& s, int rank, int device, const int* obst)
     CK(cudaEventCreate(&s.ev_start));
     CK(cudaEventCreate(&s.ev_stop));
     try {
-        s.plan = lbm::make_plan(P.nx, P.ny, rank, c->size, c->ctas_budget, c->ctas_budget, c->ctas_budget);
+        s.plan = lbm::make_plan(P.nx, P.ny, rank, c->size, c->ctas_budget);
     } catch (const std::exception& e) {
         return fail("%s", e.what());
     }
@@ -320,19 +316,23 @@ int slab_create(lbm_ctx* c, Slab& s, int rank, int device, const int* obst)
 
     for (int i = 0; i < 2; ++i) CK(cudaMalloc(&s.buf[i], sizeof(float) * 9 * ps));
     CK(cudaMalloc(&s.mask, (size_t)(pl.rows + 2) * pitch));
-    CK(cudaMalloc(&s.flags, sizeof(unsigned) * std::max(pl.num_flags, 1)));
+    CK(cudaMalloc(&s.flags, sizeof(unsigned) * G));
     CK(cudaMalloc(&s.partials, sizeof(double) * (size_t)std::max(P.max_iters, 1) * G));
     CK(cudaMalloc(&s.tot, sizeof(double) * std::max(P.max_iters, 1)));
     CK(cudaMalloc(&s.status, sizeof(int)));
     CK(cudaMalloc(&s.step_ptr, sizeof(int)));
     CK(cudaMalloc(&s.scal, sizeof(double) * 2));
-    CK(cudaMemsetAsync(s.flags, 0, sizeof(unsigned) * std::max(pl.num_flags, 1), s.stream));
+    CK(cudaMemsetAsync(s.flags, 0, sizeof(unsigned) * G, s.stream));
+    if (c->size > 1) {     // tag 0 = never written; the first run's tags start at 1
+        CK(cudaMalloc(&s.ll_in, sizeof(uint2) * 12 * (size_t)P.nx));
+        CK(cudaMemsetAsync(s.ll_in, 0, sizeof(uint2) * 12 * (size_t)P.nx, s.stream));
+    }
     CK(cudaMemsetAsync(s.tot, 0, sizeof(double) * std::max(P.max_iters, 1), s.stream));
     CK(cudaMemsetAsync(s.status, 0, sizeof(int), s.stream));
     CK(cudaMemsetAsync(s.step_ptr, 0, sizeof(int), s.stream));
 
     // schedule arrays, one allocation: task_order as (row, chunk) pairs first (8-byte aligned), then
-    // task_begin | n_interior | dep_begin | deps | pub_up | pub_down
+    // task_begin | n_interior | dep_begin | deps
     std::vector<int> h;
     auto put = [&h](const std::vector<int>& v) { size_t o = h.size(); h.insert(h.end(), v.begin(), v.end()); return o; };
     std::vector<int> pairs;
@@ -340,7 +340,7 @@ int slab_create(lbm_ctx* c, Slab& s, int rank, int device, const int* obst)
     for (int t : pl.task_order) { pairs.push_back(t / pl.tpr); pairs.push_back(t % pl.tpr); }
     const size_t o_to = put(pairs);
     const size_t o_tb = put(pl.task_begin), o_ni = put(pl.n_interior),
-                 o_db = put(pl.dep_begin), o_dp = put(pl.deps), o_pu = put(pl.pub_up), o_pd = put(pl.pub_down);
+                 o_db = put(pl.dep_begin), o_dp = put(pl.deps);
     h.push_back(0);
     CK(cudaMalloc(&s.sched, sizeof(int) * h.size()));
     CK(cudaMemcpyAsync(s.sched, h.data(), sizeof(int) * h.size(), cudaMemcpyHostToDevice, s.stream));
@@ -365,13 +365,19 @@ int slab_create(lbm_ctx* c, Slab& s, int rank, int device, const int* obst)
     d.omega = P.omega;
     d.aw1 = P.density * P.accel / 9.f;       // d2q9-bgk.c:237
     d.aw2 = P.density * P.accel / 36.f;      // d2q9-bgk.c:238
-    d.up_buf[0] = d.up_buf[1] = d.down_buf[0] = d.down_buf[1] = nullptr;
-    d.up_ps = d.down_ps = 0; d.down_rows = pl.rows_down;
+    d.ll_in = s.ll_in; d.ll_up = d.ll_down = nullptr;
     d.task_begin = s.sched + o_tb; d.n_interior = s.sched + o_ni; d.task_order = (const int2*)(s.sched + o_to);
-    d.dep_begin = s.sched + o_db; d.deps = s.sched + o_dp; d.pub_up = s.sched + o_pu; d.pub_down = s.sched + o_pd;
-    d.flags = s.flags; d.up_flags = d.down_flags = nullptr;
+    d.dep_begin = s.sched + o_db; d.deps = s.sched + o_dp;
+    d.flags = s.flags;
     d.num_ctas = G;
     d.partials = s.partials; d.tot = s.tot; d.status = s.status;
+    d.prof = nullptr;
+    if (env_int("LBM_PROFILE", 0)) {
+        const size_t n = sizeof(long long) * (size_t)G * lbm::kMaxWarps * 4;
+        CK(cudaMalloc(&s.prof, n));
+        CK(cudaMemset(s.prof, 0, n));
+        d.prof = s.prof;
+    }
     return 0;
 }
 
@@ -436,37 +442,15 @@ int lbm_allocate_rows(int ny, int size, int rank, int* row_start, int* rows)
 int lbm_plan_selftest(int nx, int ny, int size, int ctas)
 {
     try {
-        std::vector<lbm::SlabPlan> plans;
+        int next_row = 0;
         for (int r = 0; r < size; ++r) {
-            plans.push_back(lbm::make_plan(nx, ny, r, size, ctas, ctas, ctas));
-            const std::string e = lbm::validate_plan(plans.back());
+            const lbm::SlabPlan p = lbm::make_plan(nx, ny, r, size, ctas);
+            const std::string e = lbm::validate_plan(p);
             if (!e.empty()) return fail("plan of rank %d/%d invalid: %s", r, size, e.c_str());
+            if (p.row_start != next_row) return fail("rank %d: slabs do not tile the rows", r);
+            next_row += p.rows;
         }
-        if (size == 1) return 0;
-        for (int r = 0; r < size; ++r) {   // mirror indices must land in the neighbour's mirror sections
-            const lbm::SlabPlan& p = plans[r];
-            const lbm::SlabPlan& up = plans[(r + 1) % size];
-            const lbm::SlabPlan& dn = plans[(r - 1 + size) % size];
-            if (p.ctas_up != up.num_ctas || p.ctas_down != dn.num_ctas) return fail("rank %d: neighbour CTA counts disagree", r);
-            for (int b = 0; b < p.num_ctas; ++b) {
-                const lbm::Layout L = lbm::make_layout(p.tpr, p.rows, p.num_ctas);
-                bool owns_first = false, owns_last = false;
-                for (int ch = 0; ch < p.tpr; ++ch) {
-                    owns_first = owns_first || L.owner(0, ch) == b;
-                    owns_last = owns_last || L.owner(p.rows - 1, ch) == b;
-                }
-                if ((p.pub_down[b] >= 0) != owns_first || (p.pub_up[b] >= 0) != owns_last)
-                    return fail("rank %d cta %d: publish flags do not match row ownership", r, b);
-                if (owns_first) {   // I am in dn's up_owners section
-                    const int i = p.pub_down[b] - dn.num_ctas;
-                    if (i < 0 || i >= (int)dn.up_owners.size() || dn.up_owners[i] != b) return fail("rank %d cta %d: bad pub_down", r, b);
-                }
-                if (owns_last) {    // I am in up's down_owners section
-                    const int i = p.pub_up[b] - up.num_ctas - (int)up.up_owners.size();
-                    if (i < 0 || i >= (int)up.down_owners.size() || up.down_owners[i] != b) return fail("rank %d cta %d: bad pub_up", r, b);
-                }
-            }
-        }
+        if (next_row != ny) return fail("slabs cover %d of %d rows", next_row, ny);
     } catch (const std::exception& e) {
         return fail("%s", e.what());
     }
@@ -545,10 +529,8 @@ int lbm_create(lbm_ctx** out, const lbm_params* params, const int* obstacles, in
             if (e == cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError();
             else if (e != cudaSuccess) { rc = fail("cudaDeviceEnablePeerAccess: %s", cudaGetErrorString(e)); break; }
         }
-        SlabDev& d = s.dev;
-        d.up_buf[0] = up.buf[0]; d.up_buf[1] = up.buf[1]; d.up_ps = up.dev.ps; d.up_flags = up.flags;
-        d.down_buf[0] = dn.buf[0]; d.down_buf[1] = dn.buf[1]; d.down_ps = dn.dev.ps; d.down_flags = dn.flags;
-        d.down_rows = dn.plan.rows;
+        s.dev.ll_up = up.ll_in;
+        s.dev.ll_down = dn.ll_in;
     }
     if (rc) { lbm_destroy(c); return 1; }
     c->connected = true;
@@ -568,6 +550,26 @@ int lbm_transfer_bytes(const lbm_ctx* c, long long* h2d, long long* d2h)
     if (!c) return fail("ctx is NULL");
     if (h2d) *h2d = c->h2d_bytes;
     if (d2h) *d2h = c->d2h_bytes;
+    return 0;
+}
+
+int lbm_get_profile(lbm_ctx* c, int slab, long long* out, int capacity, int* num_ctas, int* warps)
+{
+    if (!c || slab < 0 || slab >= c->nslabs) return fail("lbm_get_profile: bad slab index");
+    Slab& s = c->slabs[slab];
+    if (!s.prof) return fail("lbm_get_profile: profiling is off (set LBM_PROFILE=1 before lbm_create)");
+    if (lbm_sync(c)) return 1;
+    const int G = s.plan.num_ctas, nw = c->threads / 32;
+    if (num_ctas) *num_ctas = G;
+    if (warps) *warps = nw;
+    if (!out) return 0;
+    if (capacity < G * nw * 4) return fail("lbm_get_profile: need room for %d values", G * nw * 4);
+    std::vector<long long> h((size_t)G * lbm::kMaxWarps * 4);
+    CK(cudaSetDevice(s.device));
+    CK(cudaMemcpy(h.data(), s.prof, sizeof(long long) * h.size(), cudaMemcpyDeviceToHost));
+    for (int b = 0; b < G; ++b)
+        for (int w = 0; w < nw; ++w)
+            for (int i = 0; i < 4; ++i) out[((size_t)b * nw + w) * 4 + i] = h[((size_t)b * lbm::kMaxWarps + w) * 4 + i];
     return 0;
 }
 
@@ -846,13 +848,11 @@ int lbm_total_density(lbm_ctx* c, float* out)
 }
 
 // =========================================================================== rank mode
-// Blob layout: magic, rank, size, rows, num_ctas, num_flags, plane stride, then three IPC handles.
+// Blob layout: magic, rank, size, nx, then the IPC handle of the slab's inbound halo slots.
 struct IpcBlob {
     unsigned magic;
-    int rank, size, rows, num_ctas, num_flags, nx, pad;
-    long long ps;
-    cudaIpcMemHandle_t buf[2];
-    cudaIpcMemHandle_t flags;
+    int rank, size, nx;
+    cudaIpcMemHandle_t ll_in;
 };
 static_assert(sizeof(IpcBlob) <= LBM_IPC_BLOB_BYTES, "IPC blob too large");
 
@@ -884,12 +884,9 @@ int lbm_rank_export(lbm_ctx* c, void* blob)
     CK(cudaSetDevice(s.device));
     IpcBlob b;
     memset(&b, 0, sizeof(b));
-    b.magic = 0x4C424D31u;  // "LBM1"
-    b.rank = c->rank0; b.size = c->size; b.rows = s.plan.rows; b.num_ctas = s.plan.num_ctas;
-    b.num_flags = s.plan.num_flags; b.nx = c->prm.nx; b.ps = s.dev.ps;
-    CK(cudaIpcGetMemHandle(&b.buf[0], s.buf[0]));
-    CK(cudaIpcGetMemHandle(&b.buf[1], s.buf[1]));
-    CK(cudaIpcGetMemHandle(&b.flags, s.flags));
+    b.magic = 0x4C424D32u;  // "LBM2"
+    b.rank = c->rank0; b.size = c->size; b.nx = c->prm.nx;
+    if (c->size > 1) CK(cudaIpcGetMemHandle(&b.ll_in, s.ll_in));
     memset(blob, 0, LBM_IPC_BLOB_BYTES);
     memcpy(blob, &b, sizeof(b));
     return 0;
@@ -906,26 +903,16 @@ int lbm_rank_connect(lbm_ctx* c, const void* blob_up, const void* blob_down)
     memcpy(&up, blob_up, sizeof(up));
     memcpy(&dn, blob_down, sizeof(dn));
     const int r_up = (c->rank0 + 1) % c->size, r_dn = (c->rank0 - 1 + c->size) % c->size;
-    if (up.magic != 0x4C424D31u || dn.magic != 0x4C424D31u) return fail("lbm_rank_connect: bad blob magic");
+    if (up.magic != 0x4C424D32u || dn.magic != 0x4C424D32u) return fail("lbm_rank_connect: bad blob magic");
     if (up.rank != r_up || dn.rank != r_dn || up.size != c->size || dn.size != c->size)
         return fail("lbm_rank_connect: blobs are from ranks %d/%d, expected up=%d down=%d", up.rank, dn.rank, r_up, r_dn);
-    if (up.rows != s.plan.rows_up || dn.rows != s.plan.rows_down || up.num_ctas != s.plan.ctas_up ||
-        dn.num_ctas != s.plan.ctas_down || up.nx != c->prm.nx || dn.nx != c->prm.nx)
-        return fail("lbm_rank_connect: neighbour decomposition differs from the local plan (heterogeneous GPUs?)");
+    if (up.nx != c->prm.nx || dn.nx != c->prm.nx) return fail("lbm_rank_connect: neighbour lattice width differs");
     const bool same = (r_up == r_dn);   // size == 2: both neighbours are the same process
-    for (int i = 0; i < 2; ++i) {
-        CK(cudaIpcOpenMemHandle(&s.ipc_up_buf[i], up.buf[i], cudaIpcMemLazyEnablePeerAccess));
-        if (same) s.ipc_down_buf[i] = s.ipc_up_buf[i];
-        else CK(cudaIpcOpenMemHandle(&s.ipc_down_buf[i], dn.buf[i], cudaIpcMemLazyEnablePeerAccess));
-    }
-    CK(cudaIpcOpenMemHandle(&s.ipc_up_flags, up.flags, cudaIpcMemLazyEnablePeerAccess));
-    if (same) s.ipc_down_flags = s.ipc_up_flags;
-    else CK(cudaIpcOpenMemHandle(&s.ipc_down_flags, dn.flags, cudaIpcMemLazyEnablePeerAccess));
-    SlabDev& d = s.dev;
-    d.up_buf[0] = (float*)s.ipc_up_buf[0]; d.up_buf[1] = (float*)s.ipc_up_buf[1]; d.up_ps = up.ps;
-    d.down_buf[0] = (float*)s.ipc_down_buf[0]; d.down_buf[1] = (float*)s.ipc_down_buf[1]; d.down_ps = dn.ps;
-    d.up_flags = (unsigned*)s.ipc_up_flags; d.down_flags = (unsigned*)s.ipc_down_flags;
-    d.down_rows = dn.rows;
+    CK(cudaIpcOpenMemHandle(&s.ipc_ll_up, up.ll_in, cudaIpcMemLazyEnablePeerAccess));
+    if (same) s.ipc_ll_down = s.ipc_ll_up;
+    else CK(cudaIpcOpenMemHandle(&s.ipc_ll_down, dn.ll_in, cudaIpcMemLazyEnablePeerAccess));
+    s.dev.ll_up = (uint2*)s.ipc_ll_up;
+    s.dev.ll_down = (uint2*)s.ipc_ll_down;
     c->connected = true;
     return 0;
 }

@@ -39,41 +39,93 @@ __device__ __forceinline__ TaskGeom task_geom(const SlabDev& d, int2 td, int lan
     return g;
 }
 
+constexpr long long kSpinLimitCycles = 4000000000LL;   // ~2 s: a neighbour that never arrives
+
+// Slot base of (parity, side) in an inbound halo-slot array (see "halo slots" in lbm_device.cuh).
+__device__ __forceinline__ long long ll_slot(const SlabDev& d, int par, int side) { return (long long)((par * 2 + side) * 3) * d.nx; }
+
+// Pulls the three crossing populations of one edge row for this lane's 4 cells (plus the single
+// element west / east of the warp's range for the lanes that need it) out of the local inbound
+// slots, spinning until every pair carries `tag`.  jw / je: which of the three populations is the
+// one shifted from x-1 / x+1.  Warp-uniform: all 32 lanes call it.
+__device__ __forceinline__ void ll_pull(const SlabDev& d, const uint2* base, const TaskGeom& g, unsigned tag,
+                                        int jw, int je, float4 (&v)[3], float& w, float& e)
+{
+    const unsigned nx = (unsigned)d.nx;
+    const unsigned row0 = g.rc - (unsigned)g.xc;
+    const unsigned xw = g.wc - row0, xe = g.ec - row0;
+    const long long t0 = clock64();
+    for (;;) {
+        bool ok = true;
+#pragma unroll
+        for (int j = 0; j < 3; ++j) {
+            const uint4 a = ld_volatile4(base + j * nx + g.xc), b = ld_volatile4(base + j * nx + g.xc + 2);
+            ok = ok && a.y == tag && a.w == tag && b.y == tag && b.w == tag;
+            v[j] = make_float4(__uint_as_float(a.x), __uint_as_float(a.z), __uint_as_float(b.x), __uint_as_float(b.z));
+        }
+        if (g.need_w) { const uint2 q = ld_volatile2(base + jw * nx + xw); ok = ok && q.y == tag; w = __uint_as_float(q.x); }
+        if (g.need_e) { const uint2 q = ld_volatile2(base + je * nx + xe); ok = ok && q.y == tag; e = __uint_as_float(q.x); }
+        if (__all_sync(0xffffffffu, ok)) break;
+        // give up warp-uniformly (another CTA failed, or the neighbour never arrives)
+        const bool late = clock64() - t0 > kSpinLimitCycles;
+        if (late) atomicExch(d.status, 2);
+        if (__any_sync(0xffffffffu, late || *(volatile int*)d.status != 0)) break;
+        __nanosleep(40);
+    }
+}
+
 // Updates the 4 cells of this lane for one task: pull (propagate), rebound / collision,
 // optional accelerate_flow epilogue for the NEXT step on row ny-2, store, halo push to the
 // ring neighbours, and returns the lane's sum of |u| over its fluid cells.
+// tag: the step tag the inbound halo slots must carry (multi-slab only); pushes carry tag + 1.
 template <bool S>
-__device__ __forceinline__ float process_task(const SlabDev& d, int par, int2 td, int lane, bool epilogue_accel)
+__device__ __forceinline__ float process_task(const SlabDev& d, int par, int2 td, int lane, bool epilogue_accel, unsigned tag,
+                                            long long* ll_cycles = nullptr)
 {
     const TaskGeom g = task_geom(d, td, lane);
     const float* __restrict__ src = d.buf[par];
     float* __restrict__ dst = d.buf[par ^ 1];
     const unsigned ps = (unsigned)d.ps;
+    // slab edge rows take the row beyond the edge from the inbound halo slots (warp-uniform)
+    const bool ll_s = !d.wrap_y && g.lr == 0;
+    const bool ll_n = !d.wrap_y && g.lr == d.rows - 1;
 
     // ---- 9 aligned 128-bit loads (all issued before first use)
     const float4 c0 = ld_cg4(src + (g.rc));
     const float4 c1 = ld_cg4(src + (1u * ps + g.rc));
     const float4 c3 = ld_cg4(src + (3u * ps + g.rc));
-    const float4 s2 = ld_cg4(src + (2u * ps + g.rs));
-    const float4 s5 = ld_cg4(src + (5u * ps + g.rs));
-    const float4 s6 = ld_cg4(src + (6u * ps + g.rs));
-    const float4 n4 = ld_cg4(src + (4u * ps + g.rn));
-    const float4 n7 = ld_cg4(src + (7u * ps + g.rn));
-    const float4 n8 = ld_cg4(src + (8u * ps + g.rn));
+    float4 sv[3], nv[3];      // f2,f5,f6 of the south row; f4,f7,f8 of the north row
+    if (!ll_s) {
+        sv[0] = ld_cg4(src + (2u * ps + g.rs));
+        sv[1] = ld_cg4(src + (5u * ps + g.rs));
+        sv[2] = ld_cg4(src + (6u * ps + g.rs));
+    }
+    if (!ll_n) {
+        nv[0] = ld_cg4(src + (4u * ps + g.rn));
+        nv[1] = ld_cg4(src + (7u * ps + g.rn));
+        nv[2] = ld_cg4(src + (8u * ps + g.rn));
+    }
     // ---- the elements that cross the warp's x range (one lane each side)
     float w1 = 0.f, w5 = 0.f, w8 = 0.f, e3 = 0.f, e6 = 0.f, e7 = 0.f;
     if (g.need_w) {
         w1 = ld_cg1(src + (1u * ps + g.wc));
-        w5 = ld_cg1(src + (5u * ps + g.ws));
-        w8 = ld_cg1(src + (8u * ps + g.wn));
+        if (!ll_s) w5 = ld_cg1(src + (5u * ps + g.ws));
+        if (!ll_n) w8 = ld_cg1(src + (8u * ps + g.wn));
     }
     if (g.need_e) {
         e3 = ld_cg1(src + (3u * ps + g.ec));
-        e6 = ld_cg1(src + (6u * ps + g.es));
-        e7 = ld_cg1(src + (7u * ps + g.en));
+        if (!ll_s) e6 = ld_cg1(src + (6u * ps + g.es));
+        if (!ll_n) e7 = ld_cg1(src + (7u * ps + g.en));
     }
     const unsigned mbyte = __ldg(d.mask + ((unsigned)(g.lr + 1) * (unsigned)d.mask_pitch + ((unsigned)g.xc >> 3)));
     const unsigned nib = (mbyte >> (g.xc & 4)) & 0xFu;
+    if (ll_s | ll_n) {
+        const long long t0 = ll_cycles ? clock64() : 0;
+        if (ll_s) ll_pull(d, d.ll_in + ll_slot(d, par, 0), g, tag, 1, 2, sv, w5, e6);
+        if (ll_n) ll_pull(d, d.ll_in + ll_slot(d, par, 1), g, tag, 2, 1, nv, w8, e7);
+        if (ll_cycles) *ll_cycles += clock64() - t0;
+    }
+    const float4 s2 = sv[0], s5 = sv[1], s6 = sv[2], n4 = nv[0], n7 = nv[1], n8 = nv[2];
 
     // ---- lane-crossing elements by shuffle
     const unsigned full = 0xffffffffu;
@@ -111,16 +163,15 @@ __device__ __forceinline__ float process_task(const SlabDev& d, int par, int2 td
         for (int k = 0; k < 9; ++k) o[k] = make_float4(p[0][k], p[1][k], p[2][k], p[3][k]);
 #pragma unroll
         for (int k = 0; k < 9; ++k) st_cg4(dst + ((unsigned)k * ps + g.rc), o[k]);
-        if (!d.wrap_y) {
-            // halo push over NVLink: only the three populations that cross the slab edge
-            if (g.lr == d.rows - 1) {          // my top row -> up neighbour's bottom halo (row 0)
-                float* u = d.up_buf[par ^ 1] + g.x0;
-                st_cg4(u + 2 * d.up_ps, o[2]); st_cg4(u + 5 * d.up_ps, o[5]); st_cg4(u + 6 * d.up_ps, o[6]);
-            }
-            if (g.lr == 0) {                   // my bottom row -> down neighbour's top halo
-                float* w = d.down_buf[par ^ 1] + (long long)(d.down_rows + 1) * d.nx + g.x0;
-                st_cg4(w + 4 * d.down_ps, o[4]); st_cg4(w + 7 * d.down_ps, o[7]); st_cg4(w + 8 * d.down_ps, o[8]);
-            }
+        // halo push over NVLink: only the three populations that cross the slab edge, as
+        // (value, tag) pairs into the ring neighbour's inbound slots of the other parity
+        if (ll_n) {          // my top row -> the up neighbour's side 0 (row below its first row)
+            uint2* u = d.ll_up + ll_slot(d, par ^ 1, 0) + g.x0;
+            st_pairs(u, o[2], tag + 1u); st_pairs(u + d.nx, o[5], tag + 1u); st_pairs(u + 2 * d.nx, o[6], tag + 1u);
+        }
+        if (ll_s) {          // my bottom row -> the down neighbour's side 1 (row above its last row)
+            uint2* w = d.ll_down + ll_slot(d, par ^ 1, 1) + g.x0;
+            st_pairs(w, o[4], tag + 1u); st_pairs(w + d.nx, o[7], tag + 1u); st_pairs(w + 2 * d.nx, o[8], tag + 1u);
         }
     } else {
         usum = 0.f;
@@ -128,9 +179,9 @@ __device__ __forceinline__ float process_task(const SlabDev& d, int par, int2 td
     return usum;
 }
 
-// accelerate_flow (d2q9-bgk.c:235-266) applied IN PLACE to one task of row ny-2 of buffer `par`,
-// with the halo push of the touched populations.  Used once per lbm_run, before its first step;
-// later steps get the body force through process_task's epilogue.
+// accelerate_flow (d2q9-bgk.c:235-266) applied IN PLACE to one task of row ny-2 of buffer `par`.
+// Used once per lbm_run, before its first step; later steps get the body force through
+// process_task's epilogue.
 __device__ __forceinline__ void accelerate_task(const SlabDev& d, int par, int2 td, int lane)
 {
     const TaskGeom g = task_geom(d, td, lane);
@@ -157,15 +208,24 @@ __device__ __forceinline__ void accelerate_task(const SlabDev& d, int par, int2 
         v[k] = make_float4(p[0][k], p[1][k], p[2][k], p[3][k]);
         st_cg4(b + k * d.ps + off, v[k]);
     }
-    if (!d.wrap_y) {
-        if (g.lr == d.rows - 1) {
-            float* u = d.up_buf[par] + g.x0;
-            st_cg4(u + 5 * d.up_ps, v[5]); st_cg4(u + 6 * d.up_ps, v[6]);
-        }
-        if (g.lr == 0) {
-            float* w = d.down_buf[par] + (long long)(d.down_rows + 1) * d.nx + g.x0;
-            st_cg4(w + 7 * d.down_ps, v[7]); st_cg4(w + 8 * d.down_ps, v[8]);
-        }
+}
+
+// Start of a run: (re)publishes one task of a slab edge row of buffer `par` into the ring
+// neighbour's inbound slots with the run's first tag, so that every lbm_run starts from what the
+// lattice holds (initial state, lbm_set_cells, or the previous run's result + accelerate prologue).
+// Must be called by the same lanes that ran accelerate_task on this task, after it.
+__device__ __forceinline__ void publish_edge_task(const SlabDev& d, int par, int2 td, int lane, unsigned tag)
+{
+    const TaskGeom g = task_geom(d, td, lane);
+    if (!g.active) return;
+    const float* b = d.buf[par] + g.rc;
+    if (g.lr == d.rows - 1) {
+        uint2* u = d.ll_up + ll_slot(d, par, 0) + g.x0;
+        st_pairs(u, ld_cg4(b + 2 * d.ps), tag); st_pairs(u + d.nx, ld_cg4(b + 5 * d.ps), tag); st_pairs(u + 2 * d.nx, ld_cg4(b + 6 * d.ps), tag);
+    }
+    if (g.lr == 0) {
+        uint2* w = d.ll_down + ll_slot(d, par, 1) + g.x0;
+        st_pairs(w, ld_cg4(b + 4 * d.ps), tag); st_pairs(w + d.nx, ld_cg4(b + 7 * d.ps), tag); st_pairs(w + 2 * d.nx, ld_cg4(b + 8 * d.ps), tag);
     }
 }
 
@@ -189,7 +249,7 @@ __global__ void __launch_bounds__(256) lbm_step_kernel(SlabDev d, int par, const
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
     const int task = blockIdx.x * nw + warp;
     double s = 0.0;
-    if (task < d.rows * d.tpr) s = (double)process_task<S>(d, par, __ldg(d.task_order + task), lane, epilogue_accel != 0);
+    if (task < d.rows * d.tpr) s = (double)process_task<S>(d, par, __ldg(d.task_order + task), lane, epilogue_accel != 0, 0u);
     s = warp_sum(s);
     if (lane == 0) red[warp] = s;
     __syncthreads();
@@ -213,23 +273,21 @@ __global__ void lbm_advance_step_kernel(int* step_ptr, int n) { *step_ptr += n; 
 // ------------------------------------------------------------------------------------------
 // Engine 1: persistent, neighbour-synchronised.  Launched cooperatively (for the
 // co-residency guarantee only; there is NO grid-wide barrier).  Every CTA owns a fixed set of
-// tasks, loops over all `iters` timesteps and synchronises only with the CTAs (local, or on
-// the ring-neighbour GPUs through mirrored flags) that own adjacent tasks.
-//   progress value of a CTA = base + 1 after the accelerate prologue, base + 1 + (s+1) after
-//   local step s.  Boundary tasks of step s wait for all dependencies to reach base + 1 + s.
+// tasks, loops over all `iters` timesteps and synchronises only with the CTAs of its own GPU
+// that own adjacent tasks (progress flags); the ring-neighbour GPUs are coupled through the
+// tagged halo slots alone.
+//   progress value of a CTA = base + 1 after the prologue, base + 1 + (s+1) after local step s.
+//   Boundary tasks of step s wait for all dependencies to reach base + 1 + s; the same value is
+//   the tag that step s expects on its inbound halo slots.
 // ------------------------------------------------------------------------------------------
-constexpr long long kSpinLimitCycles = 4000000000LL;   // ~2 s: a neighbour that never arrives
-
 __device__ __forceinline__ bool wait_deps(const SlabDev& d, int dep_lo, int dep_hi, unsigned target, int lane)
 {
     bool ok = true;
     for (int i = dep_lo + lane; i < dep_hi; i += 32) {
-        const int idx = __ldg(d.deps + i);
-        const unsigned* f = d.flags + idx;
-        const bool remote = idx >= d.num_ctas;
+        const unsigned* f = d.flags + __ldg(d.deps + i);
         const long long t0 = clock64();
         for (;;) {
-            const unsigned v = remote ? ld_acquire_sys(f) : ld_acquire_gpu(f);
+            const unsigned v = ld_acquire_gpu(f);
             if ((int)(v - target) >= 0) break;
             if (*(volatile int*)d.status != 0) { ok = false; break; }
             if (clock64() - t0 > kSpinLimitCycles) { atomicExch(d.status, 2); ok = false; break; }
@@ -249,27 +307,22 @@ __global__ void __launch_bounds__(512, 1) lbm_persistent_kernel(SlabDev d, int p
     const int t_lo = __ldg(d.task_begin + b), t_hi = __ldg(d.task_begin + b + 1);
     const int n_int = __ldg(d.n_interior + b);
     const int dep_lo = __ldg(d.dep_begin + b), dep_hi = __ldg(d.dep_begin + b + 1);
-    const int pub_up = d.wrap_y ? -1 : __ldg(d.pub_up + b);
-    const int pub_down = d.wrap_y ? -1 : __ldg(d.pub_down + b);
     const int n_tasks = t_hi - t_lo;
+    const bool prof = d.prof != nullptr;
+    long long c_wait = 0, c_bar = 0, c_pub = 0;
+    const long long c_begin = prof ? clock64() : 0;
 
-    // ---- prologue: accelerate_flow for the first step of this run, in place
-    if (d.accel_lr >= 0) {
+    // ---- prologue: accelerate_flow for the first step of this run, in place; edge rows of a
+    // slab are (re)published to the ring neighbours with the run's first tag
+    if (d.accel_lr >= 0 || !d.wrap_y) {
         for (int k = warp; k < n_tasks; k += nw) {
             const int2 td = __ldg(d.task_order + t_lo + k);
             if (td.x == d.accel_lr) accelerate_task(d, par0, td, lane);
+            if (!d.wrap_y && (td.x == 0 || td.x == d.rows - 1)) publish_edge_task(d, par0, td, lane, base + 1u);
         }
     }
     __syncthreads();
-    if (threadIdx.x == 0) {
-        const unsigned v = base + 1u;
-        if (pub_up >= 0 || pub_down >= 0) {
-            __threadfence_system();
-            if (pub_up >= 0) st_release_sys(d.up_flags + pub_up, v);
-            if (pub_down >= 0) st_release_sys(d.down_flags + pub_down, v);
-        }
-        st_release_gpu(d.flags + b, v);
-    }
+    if (threadIdx.x == 0) st_release_gpu(d.flags + b, base + 1u);
 
     int par = par0;
     for (int s = 0; s < iters; ++s) {
@@ -279,28 +332,31 @@ __global__ void __launch_bounds__(512, 1) lbm_persistent_kernel(SlabDev d, int p
         bool waited = false;
         for (int k = warp; k < n_tasks; k += nw) {
             if (k >= n_int && !waited) {
+                const long long t0 = prof ? clock64() : 0;
                 wait_deps(d, dep_lo, dep_hi, target, lane);
+                if (prof) c_wait += clock64() - t0;
                 waited = true;
             }
             const int2 td = __ldg(d.task_order + t_lo + k);
-            acc += (double)process_task<S>(d, par, td, lane, epi);
+            acc += (double)process_task<S>(d, par, td, lane, epi, target, prof ? &c_pub : nullptr);
         }
         acc = warp_sum(acc);
         if (lane == 0) red[s & 1][warp] = acc;
+        const long long t1 = prof ? clock64() : 0;
         __syncthreads();
+        const long long t2 = prof ? clock64() : 0;
+        c_bar += t2 - t1;
         if (threadIdx.x == 0) {
             double t = 0.0;
             for (int w = 0; w < nw; ++w) t += red[s & 1][w];
             d.partials[(long long)(step0 + s) * d.num_ctas + b] = t;
-            const unsigned v = target + 1u;
-            if (pub_up >= 0 || pub_down >= 0) {
-                __threadfence_system();
-                if (pub_up >= 0) st_release_sys(d.up_flags + pub_up, v);
-                if (pub_down >= 0) st_release_sys(d.down_flags + pub_down, v);
-            }
-            st_release_gpu(d.flags + b, v);
+            st_release_gpu(d.flags + b, target + 1u);
         }
         par ^= 1;
+    }
+    if (prof && lane == 0) {
+        long long* o = d.prof + ((long long)b * kMaxWarps + warp) * 4;
+        o[0] = c_wait; o[1] = c_bar; o[2] = c_pub; o[3] = clock64() - c_begin;
     }
 }
 

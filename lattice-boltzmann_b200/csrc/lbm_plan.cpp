@@ -96,43 +96,18 @@ Layout make_layout(int tpr, int rows, int ctas)
     return best;
 }
 
-namespace {
-
-// CTAs (ascending) that own at least one task of local row `lr` of a slab.
-std::vector<int> row_owners(const Layout& L, int lr)
-{
-    std::set<int> o;
-    for (int ch = 0; ch < L.tpr; ++ch) o.insert(L.owner(lr, ch));
-    return std::vector<int>(o.begin(), o.end());
-}
-
-int index_in(const std::vector<int>& v, int x)
-{
-    auto it = std::lower_bound(v.begin(), v.end(), x);
-    if (it == v.end() || *it != x) return -1;
-    return (int)(it - v.begin());
-}
-
-}  // namespace
-
-SlabPlan make_plan(int nx, int ny, int rank, int size, int ctas, int ctas_up, int ctas_down)
+SlabPlan make_plan(int nx, int ny, int rank, int size, int ctas)
 {
     if (nx < 1 || ny < 1 || size < 1 || size > ny || rank < 0 || rank >= size || ctas < 1)
         throw std::runtime_error("make_plan: bad arguments");
     SlabPlan p;
     const SlabShape me = allocate_rows(ny, size, rank);
-    const int up = (rank + 1) % size, down = (rank - 1 + size) % size;   // d2q9-bgk.c:501-502
     p.nx = nx; p.rows = me.rows; p.row_start = me.row_start; p.rank = rank; p.size = size;
-    p.rows_up = allocate_rows(ny, size, up).rows;
-    p.rows_down = allocate_rows(ny, size, down).rows;
     p.tpr = (nx + kTaskCells - 1) / kTaskCells;
     p.num_tasks = p.tpr * p.rows;
     if (ctas > p.num_tasks) ctas = p.num_tasks;
     p.num_ctas = ctas;
     const bool single = (size == 1);
-    p.ctas_up = single ? ctas : std::min(ctas_up, p.tpr * p.rows_up);
-    p.ctas_down = single ? ctas : std::min(ctas_down, p.tpr * p.rows_down);
-    if (!single && (p.ctas_up < 1 || p.ctas_down < 1)) throw std::runtime_error("make_plan: bad neighbour ctas");
 
     // global row ny-2 receives the body force (d2q9-bgk.c:241-243, 498)
     const int ar = ny - 2;
@@ -142,39 +117,15 @@ SlabPlan make_plan(int nx, int ny, int rank, int size, int ctas, int ctas_up, in
     const int64_t T = p.num_tasks;
     const Layout L = make_layout(p.tpr, p.rows, G);
     p.strips = L.strips;
-    Layout Lup, Ldn;
-    if (!single) {
-        Lup = make_layout(p.tpr, p.rows_up, p.ctas_up);
-        Ldn = make_layout(p.tpr, p.rows_down, p.ctas_down);
-        p.up_owners = row_owners(Lup, 0);
-        p.down_owners = row_owners(Ldn, p.rows_down - 1);
-    }
-    p.num_flags = G + (int)p.up_owners.size() + (int)p.down_owners.size();
-    const int up_base = G, down_base = G + (int)p.up_owners.size();
 
     p.task_begin.assign(G + 1, 0);
     p.n_interior.assign(G, 0);
     p.dep_begin.assign(G + 1, 0);
     p.task_order.reserve(T);
-    p.pub_up.assign(G, -1);
-    p.pub_down.assign(G, -1);
-
-    std::vector<int> first_owners, last_owners;
-    int n_up_section = 0;
-    if (!single) {
-        first_owners = row_owners(L, 0);
-        last_owners = row_owners(L, p.rows - 1);
-        // The UP neighbour's flag array is [its G | its up_owners | its down_owners]; its up_owners are the
-        // first-row owners of ITS up neighbour.  All slabs are assumed to run the same CTA budget.
-        const int upup = (up + 1) % size;
-        const int rows_upup = allocate_rows(ny, size, upup).rows;
-        const int ctas_upup = std::min((upup == rank) ? G : ctas_up, p.tpr * rows_upup);
-        n_up_section = (int)row_owners(make_layout(p.tpr, rows_upup, ctas_upup), 0).size();
-    }
 
     for (int b = 0; b < G; ++b) {
         const int64_t lo = range_begin(T, G, b), hi = range_begin(T, G, b + 1);
-        std::vector<int> interior, boundary;
+        std::vector<int> interior, boundary, edge;
         std::set<int> dep;
         for (int64_t q = lo; q < hi; ++q) {
             int lr, ch;
@@ -185,36 +136,23 @@ SlabPlan make_plan(int nx, int ny, int rank, int size, int ctas, int ctas_up, in
                     const int c2 = (ch + dx + p.tpr) % p.tpr;
                     int r2 = lr + dy;
                     if (r2 < 0 || r2 >= p.rows) {
-                        if (single) {
-                            r2 = (r2 + p.rows) % p.rows;
-                        } else {
-                            // remote row: last real row of `down` (dy<0) or first real row of `up`
-                            inside = false;
-                            if (r2 < 0) dep.insert(down_base + index_in(p.down_owners, Ldn.owner(p.rows_down - 1, c2)));
-                            else dep.insert(up_base + index_in(p.up_owners, Lup.owner(0, c2)));
-                            continue;
-                        }
+                        if (!single) { inside = false; continue; }   // remote row: tagged halo slots, no flag
+                        r2 = (r2 + p.rows) % p.rows;
                     }
                     const int o = L.owner(r2, c2);
                     if (o != b) { inside = false; dep.insert(o); }
                 }
             }
-            (inside ? interior : boundary).push_back(lr * p.tpr + ch);
+            const bool is_edge = !single && (lr == 0 || lr == p.rows - 1);
+            (inside ? interior : is_edge ? edge : boundary).push_back(lr * p.tpr + ch);
         }
         p.n_interior[b] = (int)interior.size();
         p.task_order.insert(p.task_order.end(), interior.begin(), interior.end());
         p.task_order.insert(p.task_order.end(), boundary.begin(), boundary.end());
+        p.task_order.insert(p.task_order.end(), edge.begin(), edge.end());
         p.task_begin[b + 1] = (int)p.task_order.size();
         p.deps.insert(p.deps.end(), dep.begin(), dep.end());
         p.dep_begin[b + 1] = (int)p.deps.size();
-
-        if (!single) {
-            // I mirror my progress to the DOWN neighbour if I own part of my first real row (there I am in
-            // its up_owners section), and to the UP neighbour if I own part of my last real row.
-            const int i0 = index_in(first_owners, b), i1 = index_in(last_owners, b);
-            if (i0 >= 0) p.pub_down[b] = p.ctas_down + i0;
-            if (i1 >= 0) p.pub_up[b] = p.ctas_up + n_up_section + i1;
-        }
     }
     return p;
 }
@@ -230,6 +168,7 @@ std::string validate_plan(const SlabPlan& p)
         const int64_t lo = range_begin(T, G, b), hi = range_begin(T, G, b + 1);
         if (p.task_begin[b + 1] - p.task_begin[b] != hi - lo) return "task_begin mismatch";
         std::set<int> dep(p.deps.begin() + p.dep_begin[b], p.deps.begin() + p.dep_begin[b + 1]);
+        bool seen_edge = false;
         for (int k = p.task_begin[b]; k < p.task_begin[b + 1]; ++k) {
             const int t = p.task_order[k];
             if (t < 0 || t >= T) return "task id out of range";
@@ -237,6 +176,10 @@ std::string validate_plan(const SlabPlan& p)
             if (L.owner(lr, ch) != b) return "task outside owner range";
             if (seen[t]++) return "task listed twice";
             const bool is_int = (k - p.task_begin[b]) < p.n_interior[b];
+            const bool is_edge = p.size > 1 && (lr == 0 || lr == p.rows - 1);
+            if (is_edge && is_int) return "edge task scheduled as interior";
+            if (seen_edge && !is_edge) return "edge tasks must come last";
+            seen_edge = seen_edge || is_edge;
             bool all_mine = true;
             for (int dy = -1; dy <= 1; ++dy)
                 for (int dx = -1; dx <= 1; ++dx) {
@@ -244,7 +187,7 @@ std::string validate_plan(const SlabPlan& p)
                     int r2 = lr + dy;
                     if (r2 < 0 || r2 >= p.rows) {
                         if (p.size == 1) r2 = (r2 + p.rows) % p.rows;
-                        else { all_mine = false; if (is_int) return "interior task touches a remote row"; continue; }
+                        else { all_mine = false; continue; }
                     }
                     const int o = L.owner(r2, c2);
                     if (o != b) {
@@ -255,10 +198,9 @@ std::string validate_plan(const SlabPlan& p)
                 }
             if (all_mine && !is_int) return "self-contained task scheduled as boundary";
         }
-        for (int d : dep) if (d < 0 || d >= p.num_flags || d == b) return "bad dependency index";
+        for (int d : dep) if (d < 0 || d >= G || d == b) return "bad dependency index";
     }
     for (int64_t t = 0; t < T; ++t) if (seen[t] != 1) return "task missing";
-    if (p.num_flags != G + (int)p.up_owners.size() + (int)p.down_owners.size()) return "num_flags";
     return "";
 }
 

@@ -11,12 +11,14 @@
 //   interior  a task whose whole 3x3 task neighbourhood (periodic in x; periodic in y only
 //             for a single slab) is owned by the same CTA: it can be updated for step s+1
 //             as soon as the CTA itself has finished step s.
-//   boundary  every other task: needs the neighbouring CTAs (possibly on the neighbouring
-//             GPU) to have finished step s, both to read their results and to be sure they
-//             no longer read the cells this task overwrites (A/B buffers).
-//   flags     per slab: [0,G) progress of local CTAs, then mirrors of the progress of the
-//             up-neighbour's CTAs that own its first real row, then of the down-neighbour's
-//             CTAs that own its last real row (written by the peer GPU over NVLink).
+//   boundary  every other task: needs the neighbouring CTAs to have finished step s, both to read
+//             their results and to be sure they no longer read the cells this task overwrites
+//             (A/B buffers).
+//   edge      a boundary task on the first or last row of a slab that has ring neighbours: the
+//             row beyond the edge comes from the neighbouring GPU through tagged halo slots
+//             (lbm_device.cuh), which carry their own readiness - no cross-GPU flag.  Edge tasks
+//             are scheduled last in a CTA's step so the neighbour's push has a whole step to land.
+//   flags     per slab: progress of its CTAs.
 #pragma once
 #include <cstdint>
 #include <string>
@@ -61,37 +63,28 @@ struct SlabPlan {
     int tpr = 0;          // tasks per row
     int num_tasks = 0;
     int num_ctas = 0;     // G
-    int rows_up = 0, rows_down = 0;   // real rows of the ring neighbours
-    int ctas_up = 0, ctas_down = 0;   // their CTA counts
     // schedule (CSR style)
     std::vector<int> task_begin;   // G+1 offsets into task_order
     std::vector<int> n_interior;   // G: the first n_interior[b] tasks of CTA b are interior
-    std::vector<int> task_order;   // num_tasks flat task ids, interior first per CTA
+    std::vector<int> task_order;   // num_tasks flat task ids; per CTA: interior, boundary, edge
     std::vector<int> dep_begin;    // G+1 offsets into deps
-    std::vector<int> deps;         // indices into this slab's flag array
-    // mirrors
-    std::vector<int> up_owners;    // CTAs of the up neighbour owning its FIRST real row (sorted)
-    std::vector<int> down_owners;  // CTAs of the down neighbour owning its LAST real row (sorted)
-    std::vector<int> pub_up;       // G: index in the UP neighbour's flag array this CTA mirrors to, or -1
-    std::vector<int> pub_down;     // G: same for the DOWN neighbour
-    int num_flags = 0;             // G + up_owners.size() + down_owners.size()
+    std::vector<int> deps;         // CTAs (flag indices) a CTA's boundary tasks wait for
     int accel_local_row = -1;      // local real row that is global row ny-2, else -1
 };
 
 // Owner CTA of flat task `t` for an even split (inverse of range_begin).
 int owner_of(int64_t tasks, int ctas, int64_t t);
 
-// Builds the plan of slab `rank` of `size` for an nx x ny lattice, with `ctas` persistent CTAs
-// on this slab and `ctas_up` / `ctas_down` on the ring neighbours (all equal on a homogeneous
-// box).  Throws std::runtime_error on impossible arguments.
-SlabPlan make_plan(int nx, int ny, int rank, int size, int ctas, int ctas_up, int ctas_down);
+// Builds the plan of slab `rank` of `size` for an nx x ny lattice with `ctas` persistent CTAs.
+// Throws std::runtime_error on impossible arguments.
+SlabPlan make_plan(int nx, int ny, int rank, int size, int ctas);
 
 // Number of persistent CTAs to use: min(max_resident, number of tasks), at least 1.
 int choose_ctas(int nx, int rows, int max_resident);
 
 // Self-check used by the tests: every task appears exactly once, interior tasks really have
-// all neighbours inside the CTA, every neighbour owner of a boundary task is in deps, mirror
-// indices are consistent between neighbouring plans.  Returns "" or a description.
+// all neighbours inside the CTA, every neighbour owner of a boundary task is in deps, edge tasks
+// come last.  Returns "" or a description.
 std::string validate_plan(const SlabPlan& p);
 double interior_fraction(const SlabPlan& p);
 
