@@ -58,7 +58,7 @@ struct Slab {
     cudaGraphExec_t graph = nullptr;
     int graph_steps = 0;
     int graph_par = -1;
-    uint2* ll_in = nullptr;        // inbound halo slots [parity 2][side 2][pop 3][nx] (multi-slab only)
+    uint4* ll_in = nullptr;        // inbound halo slots [parity 2][side 2][record 4][nx/4] (multi-slab only)
     // IPC (one-process-per-GPU mode): the ring neighbours' inbound halo slots
     void* ipc_ll_up = nullptr;
     void* ipc_ll_down = nullptr;
@@ -83,6 +83,7 @@ struct lbm_ctx {
     bool strict = true;
     int threads = 512;
     int ctas_budget = 0;     // persistent CTAs per slab (before clamping to the task count)
+    size_t stage_bytes = 0;  // dynamic shared memory per persistent CTA
     int free_cells = 0;      // denominator of av_vels
     int blocked_cells = 0;
     float last_ms = 0.f;
@@ -283,8 +284,11 @@ int configure_engine(lbm_ctx* c, int device)
     c->threads = c->opt.threads_per_cta ? c->opt.threads_per_cta : env_int("LBM_THREADS", 256);
     if (c->threads % 32 || c->threads < 32 || c->threads > 512) return fail("threads_per_cta must be a multiple of 32 in [32,512]");
     int per_sm = c->opt.ctas_per_sm ? c->opt.ctas_per_sm : env_int("LBM_CTAS_PER_SM", 2);
+    // multi-slab: two halo stage buffers per warp in dynamic shared memory
+    c->stage_bytes = c->size > 1 ? (size_t)(c->threads / 32) * 2 * lbm::kStageRecords * sizeof(uint4) : 0;
+    CK(cudaFuncSetAttribute(persistent_fn(c->strict), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->stage_bytes));
     int occ = 0;
-    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, persistent_fn(c->strict), c->threads, 0));
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, persistent_fn(c->strict), c->threads, c->stage_bytes));
     if (occ < 1) return fail("persistent kernel does not fit on an SM with %d threads", c->threads);
     per_sm = std::max(1, std::min(per_sm, occ));
     c->ctas_budget = sms * per_sm;
@@ -298,6 +302,7 @@ int slab_create(lbm_ctx* c, Slab& s, int rank, int device, const int* obst)
     const lbm_params& P = c->prm;
     s.device = device;
     CK(cudaSetDevice(device));
+    CK(cudaFuncSetAttribute(persistent_fn(c->strict), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->stage_bytes));
     CK(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
     CK(cudaEventCreate(&s.ev_start));
     CK(cudaEventCreate(&s.ev_stop));
@@ -324,8 +329,8 @@ int slab_create(lbm_ctx* c, Slab& s, int rank, int device, const int* obst)
     CK(cudaMalloc(&s.scal, sizeof(double) * 2));
     CK(cudaMemsetAsync(s.flags, 0, sizeof(unsigned) * G, s.stream));
     if (c->size > 1) {     // tag 0 = never written; the first run's tags start at 1
-        CK(cudaMalloc(&s.ll_in, sizeof(uint2) * 12 * (size_t)P.nx));
-        CK(cudaMemsetAsync(s.ll_in, 0, sizeof(uint2) * 12 * (size_t)P.nx, s.stream));
+        CK(cudaMalloc(&s.ll_in, sizeof(uint4) * 4 * (size_t)P.nx));
+        CK(cudaMemsetAsync(s.ll_in, 0, sizeof(uint4) * 4 * (size_t)P.nx, s.stream));
     }
     CK(cudaMemsetAsync(s.tot, 0, sizeof(double) * std::max(P.max_iters, 1), s.stream));
     CK(cudaMemsetAsync(s.status, 0, sizeof(int), s.stream));
@@ -648,7 +653,7 @@ static int run_engine1(lbm_ctx* c, int iters)
         int par0 = c->par, step0 = c->steps_done, it = iters;
         unsigned base = c->base;
         void* args[] = {(void*)&s.dev, (void*)&par0, (void*)&step0, (void*)&it, (void*)&base};
-        CK(cudaLaunchCooperativeKernel(fn, dim3(s.plan.num_ctas), dim3(c->threads), args, 0, s.stream));
+        CK(cudaLaunchCooperativeKernel(fn, dim3(s.plan.num_ctas), dim3(c->threads), args, c->stage_bytes, s.stream));
         CK(cudaEventRecord(s.ev_stop, s.stream));
         ++launches;
     }
@@ -911,8 +916,8 @@ int lbm_rank_connect(lbm_ctx* c, const void* blob_up, const void* blob_down)
     CK(cudaIpcOpenMemHandle(&s.ipc_ll_up, up.ll_in, cudaIpcMemLazyEnablePeerAccess));
     if (same) s.ipc_ll_down = s.ipc_ll_up;
     else CK(cudaIpcOpenMemHandle(&s.ipc_ll_down, dn.ll_in, cudaIpcMemLazyEnablePeerAccess));
-    s.dev.ll_up = (uint2*)s.ipc_ll_up;
-    s.dev.ll_down = (uint2*)s.ipc_ll_down;
+    s.dev.ll_up = (uint4*)s.ipc_ll_up;
+    s.dev.ll_down = (uint4*)s.ipc_ll_down;
     c->connected = true;
     return 0;
 }

@@ -39,32 +39,54 @@ __device__ __forceinline__ TaskGeom task_geom(const SlabDev& d, int2 td, int lan
     return g;
 }
 
+// SM cycle counter that the compiler may not move across barriers or memory operations (profiling)
+__device__ __forceinline__ long long clock_fenced()
+{
+    long long t;
+    asm volatile("mov.u64 %0, %%clock64;" : "=l"(t)::"memory");
+    return t;
+}
+
 constexpr long long kSpinLimitCycles = 4000000000LL;   // ~2 s: a neighbour that never arrives
 
-// Slot base of (parity, side) in an inbound halo-slot array (see "halo slots" in lbm_device.cuh).
-__device__ __forceinline__ long long ll_slot(const SlabDev& d, int par, int side) { return (long long)((par * 2 + side) * 3) * d.nx; }
+// First record of (parity, side) in an inbound halo-slot array (see "halo slots" in lbm_device.cuh):
+// 4 record planes of nx/4 records each.
+__device__ __forceinline__ int ll_slot(const SlabDev& d, int par, int side) { return (par * 2 + side) * d.nx; }
+
+// The record addresses one edge task reads on side SIDE: its own group in the 4 planes, the group
+// holding the west element, the group holding the east element.
+template <int SIDE>
+__device__ __forceinline__ void ll_addresses(const SlabDev& d, const uint4* base, const TaskGeom& g, const uint4*& pq,
+                                             const uint4*& pw, const uint4*& pe)
+{
+    const int Q = d.nx >> 2;
+    const unsigned row0 = g.rc - (unsigned)g.xc;
+    pq = base + (g.xc >> 2);
+    pw = base + (SIDE ? 3 : 2) * Q + ((g.wc - row0) >> 2);
+    pe = base + (SIDE ? 1 : 2) * Q + ((g.ec - row0) >> 2);
+}
 
 // Pulls the three crossing populations of one edge row for this lane's 4 cells (plus the single
 // element west / east of the warp's range for the lanes that need it) out of the local inbound
-// slots, spinning until every pair carries `tag`.  jw / je: which of the three populations is the
-// one shifted from x-1 / x+1.  Warp-uniform: all 32 lanes call it.
-__device__ __forceinline__ void ll_pull(const SlabDev& d, const uint2* base, const TaskGeom& g, unsigned tag,
-                                        int jw, int je, float4 (&v)[3], float& w, float& e)
+// slots, spinning until every record carries `tag`.  SIDE 0: row below (f2,f5,f6: west element is
+// f5 = b3 of the group before, east element f6 = c0 of the group after); SIDE 1: row above
+// (f4,f7,f8: west element f8 = c3, east element f7 = b0).  Warp-uniform: all 32 lanes call it.
+template <int SIDE>
+__device__ __forceinline__ void ll_pull(const SlabDev& d, const uint4* base, const TaskGeom& g, unsigned tag,
+                                        float4 (&v)[3], float& w, float& e)
 {
-    const unsigned nx = (unsigned)d.nx;
-    const unsigned row0 = g.rc - (unsigned)g.xc;
-    const unsigned xw = g.wc - row0, xe = g.ec - row0;
+    const int Q = d.nx >> 2;
+    const uint4 *pq, *pw, *pe;
+    ll_addresses<SIDE>(d, base, g, pq, pw, pe);
     const long long t0 = clock64();
     for (;;) {
-        bool ok = true;
-#pragma unroll
-        for (int j = 0; j < 3; ++j) {
-            const uint4 a = ld_volatile4(base + j * nx + g.xc), b = ld_volatile4(base + j * nx + g.xc + 2);
-            ok = ok && a.y == tag && a.w == tag && b.y == tag && b.w == tag;
-            v[j] = make_float4(__uint_as_float(a.x), __uint_as_float(a.z), __uint_as_float(b.x), __uint_as_float(b.z));
-        }
-        if (g.need_w) { const uint2 q = ld_volatile2(base + jw * nx + xw); ok = ok && q.y == tag; w = __uint_as_float(q.x); }
-        if (g.need_e) { const uint2 q = ld_volatile2(base + je * nx + xe); ok = ok && q.y == tag; e = __uint_as_float(q.x); }
+        const uint4 r0 = ld_record(pq), r1 = ld_record(pq + Q), r2 = ld_record(pq + 2 * Q), r3 = ld_record(pq + 3 * Q);
+        bool ok = r0.w == tag && r1.w == tag && r2.w == tag && r3.w == tag;
+        v[0] = make_float4(__uint_as_float(r0.x), __uint_as_float(r0.y), __uint_as_float(r0.z), __uint_as_float(r1.x));
+        v[1] = make_float4(__uint_as_float(r1.y), __uint_as_float(r1.z), __uint_as_float(r2.x), __uint_as_float(r2.y));
+        v[2] = make_float4(__uint_as_float(r2.z), __uint_as_float(r3.x), __uint_as_float(r3.y), __uint_as_float(r3.z));
+        if (g.need_w) { const uint4 q = ld_record(pw); ok = ok && q.w == tag; w = __uint_as_float(SIDE ? q.z : q.y); }
+        if (g.need_e) { const uint4 q = ld_record(pe); ok = ok && q.w == tag; e = __uint_as_float(SIDE ? q.y : q.z); }
         if (__all_sync(0xffffffffu, ok)) break;
         // give up warp-uniformly (another CTA failed, or the neighbour never arrives)
         const bool late = clock64() - t0 > kSpinLimitCycles;
@@ -74,13 +96,42 @@ __device__ __forceinline__ void ll_pull(const SlabDev& d, const uint2* base, con
     }
 }
 
+// Starts the asynchronous fetch of one edge task's halo records into a shared-memory stage buffer
+// (each lane fetches exactly the records it will read itself).  The caller commits the group.
+__device__ __forceinline__ void ll_prefetch(const SlabDev& d, int par, int2 td, int lane, uint4* stage)
+{
+    const TaskGeom g = task_geom(d, td, lane);
+    const uint4 *pq, *pw, *pe;
+    if (g.lr == 0) ll_addresses<0>(d, d.ll_in + ll_slot(d, par, 0), g, pq, pw, pe);
+    else ll_addresses<1>(d, d.ll_in + ll_slot(d, par, 1), g, pq, pw, pe);
+    const int Q = d.nx >> 2;
+#pragma unroll
+    for (int r = 0; r < 4; ++r) cp_async_record(stage + r * 32 + lane, pq + r * Q);
+    if (g.need_w) cp_async_record(stage + 128, pw);
+    if (g.need_e && g.active) cp_async_record(stage + 129, pe);
+}
+
+// Takes a staged edge task out of shared memory; false if any tag is not `tag` yet.
+template <int SIDE>
+__device__ __forceinline__ bool ll_take(const uint4* stage, const TaskGeom& g, int lane, unsigned tag, float4 (&v)[3], float& w, float& e)
+{
+    const uint4 r0 = stage[lane], r1 = stage[32 + lane], r2 = stage[64 + lane], r3 = stage[96 + lane];
+    bool ok = r0.w == tag && r1.w == tag && r2.w == tag && r3.w == tag;
+    v[0] = make_float4(__uint_as_float(r0.x), __uint_as_float(r0.y), __uint_as_float(r0.z), __uint_as_float(r1.x));
+    v[1] = make_float4(__uint_as_float(r1.y), __uint_as_float(r1.z), __uint_as_float(r2.x), __uint_as_float(r2.y));
+    v[2] = make_float4(__uint_as_float(r2.z), __uint_as_float(r3.x), __uint_as_float(r3.y), __uint_as_float(r3.z));
+    if (g.need_w) { const uint4 q = stage[128]; ok = ok && q.w == tag; w = __uint_as_float(SIDE ? q.z : q.y); }
+    if (g.need_e && g.active) { const uint4 q = stage[129]; ok = ok && q.w == tag; e = __uint_as_float(SIDE ? q.y : q.z); }
+    return __all_sync(0xffffffffu, ok);
+}
+
 // Updates the 4 cells of this lane for one task: pull (propagate), rebound / collision,
-// optional accelerate_flow epilogue for the NEXT step on row ny-2, store, halo push to the
-// ring neighbours, and returns the lane's sum of |u| over its fluid cells.
-// tag: the step tag the inbound halo slots must carry (multi-slab only); pushes carry tag + 1.
+// optional accelerate_flow epilogue for the NEXT step on row ny-2, store, halo push to the ring
+// neighbours, and returns the lane's sum of |u| over its fluid cells.  On a slab edge row the row
+// beyond the edge is pulled from the inbound halo slots, which must carry `tag`; pushes carry tag + 1.
 template <bool S>
 __device__ __forceinline__ float process_task(const SlabDev& d, int par, int2 td, int lane, bool epilogue_accel, unsigned tag,
-                                            long long* ll_cycles = nullptr)
+                                            const uint4* stage = nullptr, long long* ll_cycles = nullptr)
 {
     const TaskGeom g = task_geom(d, td, lane);
     const float* __restrict__ src = d.buf[par];
@@ -121,8 +172,15 @@ __device__ __forceinline__ float process_task(const SlabDev& d, int par, int2 td
     const unsigned nib = (mbyte >> (g.xc & 4)) & 0xFu;
     if (ll_s | ll_n) {
         const long long t0 = ll_cycles ? clock64() : 0;
-        if (ll_s) ll_pull(d, d.ll_in + ll_slot(d, par, 0), g, tag, 1, 2, sv, w5, e6);
-        if (ll_n) ll_pull(d, d.ll_in + ll_slot(d, par, 1), g, tag, 2, 1, nv, w8, e7);
+        bool staged = false;       // `stage`: this task's records were prefetched into shared memory
+        if (stage) {
+            cp_async_wait_all_but_last();
+            staged = ll_s ? ll_take<0>(stage, g, lane, tag, sv, w5, e6) : ll_take<1>(stage, g, lane, tag, nv, w8, e7);
+        }
+        if (!staged) {
+            if (ll_s) ll_pull<0>(d, d.ll_in + ll_slot(d, par, 0), g, tag, sv, w5, e6);
+            if (ll_n) ll_pull<1>(d, d.ll_in + ll_slot(d, par, 1), g, tag, nv, w8, e7);
+        }
         if (ll_cycles) *ll_cycles += clock64() - t0;
     }
     const float4 s2 = sv[0], s5 = sv[1], s6 = sv[2], n4 = nv[0], n7 = nv[1], n8 = nv[2];
@@ -163,16 +221,13 @@ __device__ __forceinline__ float process_task(const SlabDev& d, int par, int2 td
         for (int k = 0; k < 9; ++k) o[k] = make_float4(p[0][k], p[1][k], p[2][k], p[3][k]);
 #pragma unroll
         for (int k = 0; k < 9; ++k) st_cg4(dst + ((unsigned)k * ps + g.rc), o[k]);
-        // halo push over NVLink: only the three populations that cross the slab edge, as
-        // (value, tag) pairs into the ring neighbour's inbound slots of the other parity
-        if (ll_n) {          // my top row -> the up neighbour's side 0 (row below its first row)
-            uint2* u = d.ll_up + ll_slot(d, par ^ 1, 0) + g.x0;
-            st_pairs(u, o[2], tag + 1u); st_pairs(u + d.nx, o[5], tag + 1u); st_pairs(u + 2 * d.nx, o[6], tag + 1u);
-        }
-        if (ll_s) {          // my bottom row -> the down neighbour's side 1 (row above its last row)
-            uint2* w = d.ll_down + ll_slot(d, par ^ 1, 1) + g.x0;
-            st_pairs(w, o[4], tag + 1u); st_pairs(w + d.nx, o[7], tag + 1u); st_pairs(w + 2 * d.nx, o[8], tag + 1u);
-        }
+        // halo push over NVLink: only the three populations that cross the slab edge, as tagged
+        // records into the ring neighbour's inbound slots of the other parity
+        const int Q = d.nx >> 2, q = g.x0 >> 2;
+        if (ll_n)            // my top row -> the up neighbour's side 0 (row below its first row)
+            st_halo(d.ll_up + ll_slot(d, par ^ 1, 0) + q, Q, o[2], o[5], o[6], tag + 1u);
+        if (ll_s)            // my bottom row -> the down neighbour's side 1 (row above its last row)
+            st_halo(d.ll_down + ll_slot(d, par ^ 1, 1) + q, Q, o[4], o[7], o[8], tag + 1u);
     } else {
         usum = 0.f;
     }
@@ -219,17 +274,14 @@ __device__ __forceinline__ void publish_edge_task(const SlabDev& d, int par, int
     const TaskGeom g = task_geom(d, td, lane);
     if (!g.active) return;
     const float* b = d.buf[par] + g.rc;
-    if (g.lr == d.rows - 1) {
-        uint2* u = d.ll_up + ll_slot(d, par, 0) + g.x0;
-        st_pairs(u, ld_cg4(b + 2 * d.ps), tag); st_pairs(u + d.nx, ld_cg4(b + 5 * d.ps), tag); st_pairs(u + 2 * d.nx, ld_cg4(b + 6 * d.ps), tag);
-    }
-    if (g.lr == 0) {
-        uint2* w = d.ll_down + ll_slot(d, par, 1) + g.x0;
-        st_pairs(w, ld_cg4(b + 4 * d.ps), tag); st_pairs(w + d.nx, ld_cg4(b + 7 * d.ps), tag); st_pairs(w + 2 * d.nx, ld_cg4(b + 8 * d.ps), tag);
-    }
+    const int Q = d.nx >> 2, q = g.x0 >> 2;
+    if (g.lr == d.rows - 1)
+        st_halo(d.ll_up + ll_slot(d, par, 0) + q, Q, ld_cg4(b + 2 * d.ps), ld_cg4(b + 5 * d.ps), ld_cg4(b + 6 * d.ps), tag);
+    if (g.lr == 0)
+        st_halo(d.ll_down + ll_slot(d, par, 1) + q, Q, ld_cg4(b + 4 * d.ps), ld_cg4(b + 7 * d.ps), ld_cg4(b + 8 * d.ps), tag);
 }
 
-// Sum of a double over the CTA; result valid in thread 0.  `red` holds kMaxWarps doubles.
+// Sum of a double over the warp.
 __device__ __forceinline__ double warp_sum(double v)
 {
 #pragma unroll
@@ -277,39 +329,45 @@ __global__ void lbm_advance_step_kernel(int* step_ptr, int n) { *step_ptr += n; 
 // that own adjacent tasks (progress flags); the ring-neighbour GPUs are coupled through the
 // tagged halo slots alone.
 //   progress value of a CTA = base + 1 after the prologue, base + 1 + (s+1) after local step s.
-//   Boundary tasks of step s wait for all dependencies to reach base + 1 + s; the same value is
-//   the tag that step s expects on its inbound halo slots.
+//   Boundary tasks of step s wait for all dependencies to reach base + 1 + s (their step s-1
+//   results are complete, and they no longer read the cells about to be overwritten); the same
+//   value is the tag step s expects on its inbound halo slots.
+// A CTA's step: interior tasks (need nobody), wait, slab-edge tasks (their halo pushes are then
+// acknowledged long before the release below, which waits for outstanding remote writes), the
+// other boundary tasks, CTA barrier, release of the progress flag.
 // ------------------------------------------------------------------------------------------
-__device__ __forceinline__ bool wait_deps(const SlabDev& d, int dep_lo, int dep_hi, unsigned target, int lane)
+__device__ __forceinline__ void wait_deps(const SlabDev& d, int dep_lo, int dep_hi, unsigned target, int lane)
 {
-    bool ok = true;
     for (int i = dep_lo + lane; i < dep_hi; i += 32) {
         const unsigned* f = d.flags + __ldg(d.deps + i);
         const long long t0 = clock64();
         for (;;) {
             const unsigned v = ld_acquire_gpu(f);
             if ((int)(v - target) >= 0) break;
-            if (*(volatile int*)d.status != 0) { ok = false; break; }
-            if (clock64() - t0 > kSpinLimitCycles) { atomicExch(d.status, 2); ok = false; break; }
+            if (*(volatile int*)d.status != 0) break;
+            if (clock64() - t0 > kSpinLimitCycles) { atomicExch(d.status, 2); break; }
             __nanosleep(20);
         }
     }
     __syncwarp();
-    return ok;
 }
 
 template <bool S>
 __global__ void __launch_bounds__(512, 1) lbm_persistent_kernel(SlabDev d, int par0, int step0, int iters, unsigned base)
 {
     __shared__ double red[2][kMaxWarps];
+    extern __shared__ uint4 ll_stage[];          // multi-slab: [warp][2][kStageRecords]
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
     const int b = blockIdx.x;
     const int t_lo = __ldg(d.task_begin + b), t_hi = __ldg(d.task_begin + b + 1);
     const int n_int = __ldg(d.n_interior + b);
     const int dep_lo = __ldg(d.dep_begin + b), dep_hi = __ldg(d.dep_begin + b + 1);
     const int n_tasks = t_hi - t_lo;
+    // edge tasks are staged one task ahead; a one-row slab needs both sides at once and just polls
+    const bool staging = !d.wrap_y && d.rows > 1;
+    uint4* const my_stage = ll_stage + warp * 2 * kStageRecords;
     const bool prof = d.prof != nullptr;
-    long long c_wait = 0, c_bar = 0, c_pub = 0;
+    long long c_wait = 0, c_bar = 0, c_ll = 0;
     const long long c_begin = prof ? clock64() : 0;
 
     // ---- prologue: accelerate_flow for the first step of this run, in place; edge rows of a
@@ -329,8 +387,20 @@ __global__ void __launch_bounds__(512, 1) lbm_persistent_kernel(SlabDev d, int p
         const bool epi = (s + 1 < iters);
         const unsigned target = base + 1u + (unsigned)s;
         double acc = 0.0;
-        bool waited = false;
-        for (int k = warp; k < n_tasks; k += nw) {
+        bool waited = false, staged = false;
+        int ord = 0;                              // ordinal of the task within this warp's step
+        for (int k = warp; k < n_tasks; k += nw, ++ord) {
+            bool staged_next = false;
+            if (staging) {
+                if (k + nw < n_tasks) {
+                    const int2 tn = __ldg(d.task_order + t_lo + k + nw);
+                    if (tn.x == 0 || tn.x == d.rows - 1) {
+                        ll_prefetch(d, par, tn, lane, my_stage + ((ord + 1) & 1) * kStageRecords);
+                        staged_next = true;
+                    }
+                }
+                cp_async_commit();               // one group per task, empty or not
+            }
             if (k >= n_int && !waited) {
                 const long long t0 = prof ? clock64() : 0;
                 wait_deps(d, dep_lo, dep_hi, target, lane);
@@ -338,14 +408,15 @@ __global__ void __launch_bounds__(512, 1) lbm_persistent_kernel(SlabDev d, int p
                 waited = true;
             }
             const int2 td = __ldg(d.task_order + t_lo + k);
-            acc += (double)process_task<S>(d, par, td, lane, epi, target, prof ? &c_pub : nullptr);
+            acc += (double)process_task<S>(d, par, td, lane, epi, target, staged ? my_stage + (ord & 1) * kStageRecords : nullptr,
+                                           prof ? &c_ll : nullptr);
+            staged = staged_next;
         }
         acc = warp_sum(acc);
         if (lane == 0) red[s & 1][warp] = acc;
-        const long long t1 = prof ? clock64() : 0;
+        const long long t1 = prof ? clock_fenced() : 0;
         __syncthreads();
-        const long long t2 = prof ? clock64() : 0;
-        c_bar += t2 - t1;
+        if (prof) c_bar += clock_fenced() - t1;
         if (threadIdx.x == 0) {
             double t = 0.0;
             for (int w = 0; w < nw; ++w) t += red[s & 1][w];
@@ -356,7 +427,7 @@ __global__ void __launch_bounds__(512, 1) lbm_persistent_kernel(SlabDev d, int p
     }
     if (prof && lane == 0) {
         long long* o = d.prof + ((long long)b * kMaxWarps + warp) * 4;
-        o[0] = c_wait; o[1] = c_bar; o[2] = c_pub; o[3] = clock64() - c_begin;
+        o[0] = c_wait; o[1] = c_bar; o[2] = c_ll; o[3] = clock64() - c_begin;
     }
 }
 

@@ -19,15 +19,6 @@ SlabShape allocate_rows(int ny, int size, int rank)
     return s;
 }
 
-int owner_of(int64_t tasks, int ctas, int64_t t)
-{
-    // smallest b with begin(b+1) > t ; begin(b) = tasks*b/ctas (floor)
-    int64_t b = (t * ctas) / tasks;
-    while (b + 1 < ctas && range_begin(tasks, ctas, (int)(b + 1)) <= t) ++b;
-    while (b > 0 && range_begin(tasks, ctas, (int)b) > t) --b;
-    return (int)b;
-}
-
 int choose_ctas(int nx, int rows, int max_resident)
 {
     const int tpr = (nx + kTaskCells - 1) / kTaskCells;
@@ -63,9 +54,22 @@ void Layout::task_at(int64_t p, int* lr, int* ch) const
     *ch = c0[s] + (int)(q % w);
 }
 
-int Layout::owner(int lr, int ch) const { return owner_of(tasks(), ctas, pos(lr, ch)); }
+int Layout::owner(int lr, int ch) const
+{
+    const int64_t q = pos(lr, ch);
+    return (int)(std::upper_bound(cut.begin(), cut.end(), q) - cut.begin()) - 1;
+}
 
-Layout make_layout(int tpr, int rows, int ctas)
+int default_edge_weight_16()
+{
+    if (const char* e = getenv("LBM_EDGE_WEIGHT_16")) {
+        const int v = atoi(e);
+        if (v >= 16 && v <= 64) return v;
+    }
+    return 24;   // an edge task costs about 1.5 ordinary ones (sweep: 16 -> 73.4, 20 -> 75.9, 24 -> 79.1, 28 -> 78.5, 32 -> 75.5 GLUPS/GPU)
+}
+
+Layout make_layout(int tpr, int rows, int ctas, bool edge_rows, int edge_weight_16)
 {
     // A CTA's patch is ~n/w rows of a strip w chunks wide; its interior is what is not on the rim (a
     // full-width strip has no left/right rim: x is periodic inside the CTA's own rows).  Measured on
@@ -93,6 +97,25 @@ Layout make_layout(int tpr, int rows, int ctas)
     best.tpr = tpr; best.rows = rows; best.ctas = ctas;
     best.c0.resize(best.strips + 1);
     for (int s = 0; s <= best.strips; ++s) best.c0[s] = (int)((int64_t)tpr * s / best.strips);
+
+    // cut the sequence into `ctas` ranges of equal weight (every range keeps at least one task)
+    const int64_t T = best.tasks();
+    const int we = (edge_rows && rows > 2) ? edge_weight_16 : 16;
+    std::vector<int64_t> cum(T + 1, 0);
+    for (int64_t q = 0; q < T; ++q) {
+        int lr, ch;
+        best.task_at(q, &lr, &ch);
+        cum[q + 1] = cum[q] + ((edge_rows && (lr == 0 || lr == rows - 1)) ? we : 16);
+    }
+    best.cut.assign(ctas + 1, 0);
+    for (int b = 1; b < ctas; ++b) {
+        const int64_t want = cum[T] * b / ctas;
+        int64_t q = std::lower_bound(cum.begin(), cum.end(), want) - cum.begin();
+        q = std::max<int64_t>(q, best.cut[b - 1] + 1);
+        q = std::min<int64_t>(q, T - (ctas - b));
+        best.cut[b] = q;
+    }
+    best.cut[ctas] = T;
     return best;
 }
 
@@ -115,7 +138,8 @@ SlabPlan make_plan(int nx, int ny, int rank, int size, int ctas)
 
     const int G = ctas;
     const int64_t T = p.num_tasks;
-    const Layout L = make_layout(p.tpr, p.rows, G);
+    p.edge_weight_16 = default_edge_weight_16();
+    const Layout L = make_layout(p.tpr, p.rows, G, !single, p.edge_weight_16);
     p.strips = L.strips;
 
     p.task_begin.assign(G + 1, 0);
@@ -124,7 +148,7 @@ SlabPlan make_plan(int nx, int ny, int rank, int size, int ctas)
     p.task_order.reserve(T);
 
     for (int b = 0; b < G; ++b) {
-        const int64_t lo = range_begin(T, G, b), hi = range_begin(T, G, b + 1);
+        const int64_t lo = L.cut[b], hi = L.cut[b + 1];
         std::vector<int> interior, boundary, edge;
         std::set<int> dep;
         for (int64_t q = lo; q < hi; ++q) {
@@ -148,8 +172,8 @@ SlabPlan make_plan(int nx, int ny, int rank, int size, int ctas)
         }
         p.n_interior[b] = (int)interior.size();
         p.task_order.insert(p.task_order.end(), interior.begin(), interior.end());
-        p.task_order.insert(p.task_order.end(), boundary.begin(), boundary.end());
         p.task_order.insert(p.task_order.end(), edge.begin(), edge.end());
+        p.task_order.insert(p.task_order.end(), boundary.begin(), boundary.end());
         p.task_begin[b + 1] = (int)p.task_order.size();
         p.deps.insert(p.deps.end(), dep.begin(), dep.end());
         p.dep_begin[b + 1] = (int)p.deps.size();
@@ -161,14 +185,15 @@ std::string validate_plan(const SlabPlan& p)
 {
     const int G = p.num_ctas;
     const int64_t T = p.num_tasks;
-    const Layout L = make_layout(p.tpr, p.rows, G);
+    const Layout L = make_layout(p.tpr, p.rows, G, p.size > 1, p.edge_weight_16);
     std::vector<int> seen(T, 0);
     if ((int)p.task_order.size() != T) return "task_order size";
     for (int b = 0; b < G; ++b) {
-        const int64_t lo = range_begin(T, G, b), hi = range_begin(T, G, b + 1);
+        const int64_t lo = L.cut[b], hi = L.cut[b + 1];
+        if (hi <= lo) return "empty CTA range";
         if (p.task_begin[b + 1] - p.task_begin[b] != hi - lo) return "task_begin mismatch";
         std::set<int> dep(p.deps.begin() + p.dep_begin[b], p.deps.begin() + p.dep_begin[b + 1]);
-        bool seen_edge = false;
+        bool seen_plain = false;
         for (int k = p.task_begin[b]; k < p.task_begin[b + 1]; ++k) {
             const int t = p.task_order[k];
             if (t < 0 || t >= T) return "task id out of range";
@@ -178,8 +203,8 @@ std::string validate_plan(const SlabPlan& p)
             const bool is_int = (k - p.task_begin[b]) < p.n_interior[b];
             const bool is_edge = p.size > 1 && (lr == 0 || lr == p.rows - 1);
             if (is_edge && is_int) return "edge task scheduled as interior";
-            if (seen_edge && !is_edge) return "edge tasks must come last";
-            seen_edge = seen_edge || is_edge;
+            if (is_edge && seen_plain) return "edge tasks must lead the boundary tasks";
+            seen_plain = seen_plain || (!is_int && !is_edge);
             bool all_mine = true;
             for (int dy = -1; dy <= 1; ++dy)
                 for (int dx = -1; dx <= 1; ++dx) {

@@ -7,7 +7,7 @@
 //             allocate_rows, d2q9-bgk.c:483-503), stored with one halo row either side.
 //   task      LBM_TASK_CELLS consecutive cells of one row = what one warp updates at a
 //             time (each lane a float4 of 4 cells).  Flat id = local_row * tpr + chunk.
-//   CTA range each persistent CTA owns a contiguous range of flat task ids.
+//   CTA range each persistent CTA owns a contiguous range of the strip-major task sequence.
 //   interior  a task whose whole 3x3 task neighbourhood (periodic in x; periodic in y only
 //             for a single slab) is owned by the same CTA: it can be updated for step s+1
 //             as soon as the CTA itself has finished step s.
@@ -17,7 +17,9 @@
 //   edge      a boundary task on the first or last row of a slab that has ring neighbours: the
 //             row beyond the edge comes from the neighbouring GPU through tagged halo slots
 //             (lbm_device.cuh), which carry their own readiness - no cross-GPU flag.  Edge tasks
-//             are scheduled last in a CTA's step so the neighbour's push has a whole step to land.
+//             lead a CTA's boundary tasks: their pushes then have the rest of the step to cross
+//             NVLink before the neighbour needs them, and are acknowledged before the CTA releases
+//             its progress flag (a release waits for outstanding remote writes).
 //   flags     per slab: progress of its CTAs.
 #pragma once
 #include <cstdint>
@@ -37,28 +39,30 @@ struct SlabShape {
 // ny/size rows each, the first ny%size ranks one more.
 SlabShape allocate_rows(int ny, int size, int rank);
 
-// Even contiguous split of `tasks` over `ctas`: CTA b owns [begin(b), begin(b+1)).
-inline int64_t range_begin(int64_t tasks, int ctas, int b) { return tasks * b / ctas; }
-
 // Ownership layout of one slab: the rows x tpr grid of tasks is cut into vertical STRIPS of about
 // `strip_w` chunks; tasks are ordered strip by strip, row-major inside a strip, and that sequence is cut
 // into `ctas` equal ranges.  Every CTA therefore owns a compact patch (a few rows of one strip) with a
 // perfectly balanced task count, and most of its tasks are interior.  strip_w == tpr is plain row-major.
 struct Layout {
     int tpr = 0, rows = 0, ctas = 0, strips = 1;
-    std::vector<int> c0;    // first chunk of strip s (size strips+1)
+    std::vector<int> c0;      // first chunk of strip s (size strips+1)
+    std::vector<int64_t> cut; // CTA b owns sequence positions [cut[b], cut[b+1])  (size ctas+1)
     int64_t tasks() const { return (int64_t)tpr * rows; }
     int strip_of(int ch) const;
     int64_t pos(int lr, int ch) const;        // position in the strip-major sequence
     void task_at(int64_t pos, int* lr, int* ch) const;
     int owner(int lr, int ch) const;
 };
-// Picks the strip count that maximises the expected number of interior tasks per CTA.
-Layout make_layout(int tpr, int rows, int ctas);
+// Picks the strip count that maximises the expected number of interior tasks per CTA and cuts the
+// sequence into `ctas` ranges of equal WEIGHT: a task counts 1, except that on a slab with ring
+// neighbours (edge_rows) the tasks of the first and last row count edge_weight_16 / 16 - they pull and
+// push tagged halo records on top of the ordinary update, and the slowest CTA paces its neighbours.
+Layout make_layout(int tpr, int rows, int ctas, bool edge_rows = false, int edge_weight_16 = 16);
+int default_edge_weight_16();   // measured on B200 (profiles/r01_sync_probe.md); env LBM_EDGE_WEIGHT_16 overrides
 
 struct SlabPlan {
     int nx = 0, rows = 0, row_start = 0;
-    int strips = 1;
+    int strips = 1, edge_weight_16 = 16;
     int rank = 0, size = 1;
     int tpr = 0;          // tasks per row
     int num_tasks = 0;
@@ -66,14 +70,11 @@ struct SlabPlan {
     // schedule (CSR style)
     std::vector<int> task_begin;   // G+1 offsets into task_order
     std::vector<int> n_interior;   // G: the first n_interior[b] tasks of CTA b are interior
-    std::vector<int> task_order;   // num_tasks flat task ids; per CTA: interior, boundary, edge
+    std::vector<int> task_order;   // num_tasks flat task ids; per CTA: interior, edge, boundary
     std::vector<int> dep_begin;    // G+1 offsets into deps
     std::vector<int> deps;         // CTAs (flag indices) a CTA's boundary tasks wait for
     int accel_local_row = -1;      // local real row that is global row ny-2, else -1
 };
-
-// Owner CTA of flat task `t` for an even split (inverse of range_begin).
-int owner_of(int64_t tasks, int ctas, int64_t t);
 
 // Builds the plan of slab `rank` of `size` for an nx x ny lattice with `ctas` persistent CTAs.
 // Throws std::runtime_error on impossible arguments.
@@ -84,7 +85,7 @@ int choose_ctas(int nx, int rows, int max_resident);
 
 // Self-check used by the tests: every task appears exactly once, interior tasks really have
 // all neighbours inside the CTA, every neighbour owner of a boundary task is in deps, edge tasks
-// come last.  Returns "" or a description.
+// lead the boundary tasks.  Returns "" or a description.
 std::string validate_plan(const SlabPlan& p);
 double interior_fraction(const SlabPlan& p);
 
