@@ -508,7 +508,7 @@ int lbm_create(lbm_ctx** out, const lbm_params* params, const int* obstacles, in
     if (create_common(out, params, obstacles, opts, &c)) return 1;
     const int ndev = lbm_device_count();
     const int first = c->opt.first_device;
-    if (ngpus <= 0) ngpus = env_int("LBM_NGPUS", ndev - first);
+    if (ngpus <= 0) ngpus = ndev - first;      // "all visible devices"
     ngpus = std::min(ngpus, params->ny);
     if (ngpus < 1 || first < 0 || first + ngpus > ndev || ngpus > LBM_MAX_GPUS) {
         fail("requested %d GPUs from device %d but %d are visible", ngpus, first, ndev);

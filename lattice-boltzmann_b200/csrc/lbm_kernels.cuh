@@ -47,7 +47,7 @@ __device__ __forceinline__ long long clock_fenced()
     return t;
 }
 
-constexpr long long kSpinLimitCycles = 4000000000LL;   // ~2 s: a neighbour that never arrives
+constexpr long long kSpinLimitCycles = 20000000000LL;  // ~10 s: a neighbour (CTA, GPU or process) that never arrives
 
 // First record of (parity, side) in an inbound halo-slot array (see "halo slots" in lbm_device.cuh):
 // 4 record planes of nx/4 records each.
