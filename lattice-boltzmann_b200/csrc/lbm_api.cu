@@ -228,9 +228,10 @@ __global__ void k_selftest_math(unsigned long long n, unsigned long long seed, i
 // =========================================================================== slab set-up
 namespace {
 
-const void* persistent_fn(bool strict)
+const void* persistent_fn(bool strict, bool ring)
 {
-    return strict ? (const void*)lbm::lbm_persistent_kernel<true> : (const void*)lbm::lbm_persistent_kernel<false>;
+    if (ring) return strict ? (const void*)lbm::lbm_persistent_kernel<true, true> : (const void*)lbm::lbm_persistent_kernel<false, true>;
+    return strict ? (const void*)lbm::lbm_persistent_kernel<true, false> : (const void*)lbm::lbm_persistent_kernel<false, false>;
 }
 
 int env_int(const char* name, int dflt)
@@ -286,9 +287,9 @@ int configure_engine(lbm_ctx* c, int device)
     int per_sm = c->opt.ctas_per_sm ? c->opt.ctas_per_sm : env_int("LBM_CTAS_PER_SM", 2);
     // multi-slab: two halo stage buffers per warp in dynamic shared memory
     c->stage_bytes = c->size > 1 ? (size_t)(c->threads / 32) * 2 * lbm::kStageRecords * sizeof(uint4) : 0;
-    CK(cudaFuncSetAttribute(persistent_fn(c->strict), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->stage_bytes));
+    CK(cudaFuncSetAttribute(persistent_fn(c->strict, c->size > 1), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->stage_bytes));
     int occ = 0;
-    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, persistent_fn(c->strict), c->threads, c->stage_bytes));
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, persistent_fn(c->strict, c->size > 1), c->threads, c->stage_bytes));
     if (occ < 1) return fail("persistent kernel does not fit on an SM with %d threads", c->threads);
     per_sm = std::max(1, std::min(per_sm, occ));
     c->ctas_budget = sms * per_sm;
@@ -302,7 +303,7 @@ int slab_create(lbm_ctx* c, Slab& s, int rank, int device, const int* obst)
     const lbm_params& P = c->prm;
     s.device = device;
     CK(cudaSetDevice(device));
-    CK(cudaFuncSetAttribute(persistent_fn(c->strict), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->stage_bytes));
+    CK(cudaFuncSetAttribute(persistent_fn(c->strict, c->size > 1), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->stage_bytes));
     CK(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
     CK(cudaEventCreate(&s.ev_start));
     CK(cudaEventCreate(&s.ev_stop));
@@ -365,7 +366,6 @@ int slab_create(lbm_ctx* c, Slab& s, int rank, int device, const int* obst)
     SlabDev& d = s.dev;
     d.buf[0] = s.buf[0]; d.buf[1] = s.buf[1];
     d.mask = s.mask; d.ps = ps; d.nx = P.nx; d.rows = pl.rows; d.tpr = pl.tpr; d.mask_pitch = pitch;
-    d.wrap_y = (c->size == 1);
     d.accel_lr = pl.accel_local_row;
     d.omega = P.omega;
     d.aw1 = P.density * P.accel / 9.f;       // d2q9-bgk.c:237
@@ -645,7 +645,7 @@ static int run_engine2(lbm_ctx* c, int iters)
 
 static int run_engine1(lbm_ctx* c, int iters)
 {
-    const void* fn = persistent_fn(c->strict);
+    const void* fn = persistent_fn(c->strict, c->size > 1);
     int launches = 0;
     for (Slab& s : c->slabs) {
         CK(cudaSetDevice(s.device));

@@ -14,6 +14,9 @@ struct TaskGeom {
     bool active, need_w, need_e;
 };
 
+// RING: the slab has ring neighbours on other GPUs (rows beyond its edges come from halo slots);
+// otherwise it is the whole lattice and y wraps inside it.
+template <bool RING>
 __device__ __forceinline__ TaskGeom task_geom(const SlabDev& d, int2 td, int lane)
 {
     TaskGeom g;
@@ -23,7 +26,7 @@ __device__ __forceinline__ TaskGeom task_geom(const SlabDev& d, int2 td, int lan
     g.xc = g.active ? g.x0 : 0;            // inactive lanes (ragged last chunk) shadow x=0, never store
     const int h = g.lr + 1;                // row index in the haloed layout
     int hs = h - 1, hn = h + 1;
-    if (d.wrap_y) {                        // single slab: periodic in y inside the slab
+    if (!RING) {                           // single slab: periodic in y inside the slab
         if (g.lr == 0) hs = d.rows;
         if (g.lr == d.rows - 1) hn = 1;
     }
@@ -100,7 +103,7 @@ __device__ __forceinline__ void ll_pull(const SlabDev& d, const uint4* base, con
 // (each lane fetches exactly the records it will read itself).  The caller commits the group.
 __device__ __forceinline__ void ll_prefetch(const SlabDev& d, int par, int2 td, int lane, uint4* stage)
 {
-    const TaskGeom g = task_geom(d, td, lane);
+    const TaskGeom g = task_geom<true>(d, td, lane);
     const uint4 *pq, *pw, *pe;
     if (g.lr == 0) ll_addresses<0>(d, d.ll_in + ll_slot(d, par, 0), g, pq, pw, pe);
     else ll_addresses<1>(d, d.ll_in + ll_slot(d, par, 1), g, pq, pw, pe);
@@ -129,17 +132,17 @@ __device__ __forceinline__ bool ll_take(const uint4* stage, const TaskGeom& g, i
 // optional accelerate_flow epilogue for the NEXT step on row ny-2, store, halo push to the ring
 // neighbours, and returns the lane's sum of |u| over its fluid cells.  On a slab edge row the row
 // beyond the edge is pulled from the inbound halo slots, which must carry `tag`; pushes carry tag + 1.
-template <bool S>
+template <bool S, bool RING>
 __device__ __forceinline__ float process_task(const SlabDev& d, int par, int2 td, int lane, bool epilogue_accel, unsigned tag,
                                             const uint4* stage = nullptr, long long* ll_cycles = nullptr)
 {
-    const TaskGeom g = task_geom(d, td, lane);
+    const TaskGeom g = task_geom<RING>(d, td, lane);
     const float* __restrict__ src = d.buf[par];
     float* __restrict__ dst = d.buf[par ^ 1];
     const unsigned ps = (unsigned)d.ps;
     // slab edge rows take the row beyond the edge from the inbound halo slots (warp-uniform)
-    const bool ll_s = !d.wrap_y && g.lr == 0;
-    const bool ll_n = !d.wrap_y && g.lr == d.rows - 1;
+    const bool ll_s = RING && g.lr == 0;
+    const bool ll_n = RING && g.lr == d.rows - 1;
 
     // ---- 9 aligned 128-bit loads (all issued before first use)
     const float4 c0 = ld_cg4(src + (g.rc));
@@ -239,7 +242,7 @@ __device__ __forceinline__ float process_task(const SlabDev& d, int par, int2 td
 // process_task's epilogue.
 __device__ __forceinline__ void accelerate_task(const SlabDev& d, int par, int2 td, int lane)
 {
-    const TaskGeom g = task_geom(d, td, lane);
+    const TaskGeom g = task_geom<true>(d, td, lane);       // only the task's own row is touched
     if (!g.active) return;
     float* b = d.buf[par];
     const long long off = (long long)g.rc;
@@ -271,7 +274,7 @@ __device__ __forceinline__ void accelerate_task(const SlabDev& d, int par, int2 
 // Must be called by the same lanes that ran accelerate_task on this task, after it.
 __device__ __forceinline__ void publish_edge_task(const SlabDev& d, int par, int2 td, int lane, unsigned tag)
 {
-    const TaskGeom g = task_geom(d, td, lane);
+    const TaskGeom g = task_geom<true>(d, td, lane);
     if (!g.active) return;
     const float* b = d.buf[par] + g.rc;
     const int Q = d.nx >> 2, q = g.x0 >> 2;
@@ -301,7 +304,7 @@ __global__ void __launch_bounds__(256) lbm_step_kernel(SlabDev d, int par, const
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
     const int task = blockIdx.x * nw + warp;
     double s = 0.0;
-    if (task < d.rows * d.tpr) s = (double)process_task<S>(d, par, __ldg(d.task_order + task), lane, epilogue_accel != 0, 0u);
+    if (task < d.rows * d.tpr) s = (double)process_task<S, false>(d, par, __ldg(d.task_order + task), lane, epilogue_accel != 0, 0u);
     s = warp_sum(s);
     if (lane == 0) red[warp] = s;
     __syncthreads();
@@ -352,7 +355,7 @@ __device__ __forceinline__ void wait_deps(const SlabDev& d, int dep_lo, int dep_
     __syncwarp();
 }
 
-template <bool S>
+template <bool S, bool RING>
 __global__ void __launch_bounds__(512, 1) lbm_persistent_kernel(SlabDev d, int par0, int step0, int iters, unsigned base)
 {
     __shared__ double red[2][kMaxWarps];
@@ -364,7 +367,7 @@ __global__ void __launch_bounds__(512, 1) lbm_persistent_kernel(SlabDev d, int p
     const int dep_lo = __ldg(d.dep_begin + b), dep_hi = __ldg(d.dep_begin + b + 1);
     const int n_tasks = t_hi - t_lo;
     // edge tasks are staged one task ahead; a one-row slab needs both sides at once and just polls
-    const bool staging = !d.wrap_y && d.rows > 1;
+    const bool staging = RING && d.rows > 1;
     uint4* const my_stage = ll_stage + warp * 2 * kStageRecords;
     const bool prof = d.prof != nullptr;
     long long c_wait = 0, c_bar = 0, c_ll = 0;
@@ -372,11 +375,11 @@ __global__ void __launch_bounds__(512, 1) lbm_persistent_kernel(SlabDev d, int p
 
     // ---- prologue: accelerate_flow for the first step of this run, in place; edge rows of a
     // slab are (re)published to the ring neighbours with the run's first tag
-    if (d.accel_lr >= 0 || !d.wrap_y) {
+    if (d.accel_lr >= 0 || RING) {
         for (int k = warp; k < n_tasks; k += nw) {
             const int2 td = __ldg(d.task_order + t_lo + k);
             if (td.x == d.accel_lr) accelerate_task(d, par0, td, lane);
-            if (!d.wrap_y && (td.x == 0 || td.x == d.rows - 1)) publish_edge_task(d, par0, td, lane, base + 1u);
+            if (RING && (td.x == 0 || td.x == d.rows - 1)) publish_edge_task(d, par0, td, lane, base + 1u);
         }
     }
     __syncthreads();
@@ -408,7 +411,7 @@ __global__ void __launch_bounds__(512, 1) lbm_persistent_kernel(SlabDev d, int p
                 waited = true;
             }
             const int2 td = __ldg(d.task_order + t_lo + k);
-            acc += (double)process_task<S>(d, par, td, lane, epi, target, staged ? my_stage + (ord & 1) * kStageRecords : nullptr,
+            acc += (double)process_task<S, RING>(d, par, td, lane, epi, target, staged ? my_stage + (ord & 1) * kStageRecords : nullptr,
                                            prof ? &c_ll : nullptr);
             staged = staged_next;
         }

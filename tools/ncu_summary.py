@@ -1,79 +1,126 @@
 #!/usr/bin/env python3
-"""Summarises ncu captures (run here, no GPU needed) into markdown for profiles/.
-
-  python tools/ncu_summary.py launches gpurun_out/launches_bench.csv
-  python tools/ncu_summary.py full gpurun_out/prof_persistent_16384x1024.ncu-rep <steps> <cells>
+"""Turns the ncu artefacts of tools/profile_r01.sh (gpurun_out/) into the tracked summaries under profiles/.
+    python tools/ncu_summary.py r01        # runs here (no GPU needed): ncu -i <rep> --page raw --csv
 """
 import csv
 import io
+import json
+import os
 import subprocess
 import sys
-from collections import defaultdict
+from collections import OrderedDict
 
-KEEP = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum",
-        "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "dram__throughput.avg.pct_of_peak_sustained_elapsed",
-        "lts__t_bytes.sum", "lts__throughput.avg.pct_of_peak_sustained_elapsed", "lts__t_sector_hit_rate.pct",
-        "l1tex__t_bytes.sum", "sm__throughput.avg.pct_of_peak_sustained_elapsed",
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+OUT = os.path.join(ROOT, "gpurun_out")
+PROF = os.path.join(ROOT, "profiles")
+
+WANT = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum",
+        "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "lts__throughput.avg.pct_of_peak_sustained_elapsed",
+        "lts__t_sector_hit_rate.pct", "sm__throughput.avg.pct_of_peak_sustained_elapsed",
         "sm__warps_active.avg.pct_of_peak_sustained_active", "smsp__issue_active.avg.pct_of_peak_sustained_active",
         "smsp__inst_executed.sum", "launch__registers_per_thread", "launch__grid_size", "launch__block_size",
         "launch__occupancy_limit_registers", "launch__waves_per_multiprocessor", "sm__cycles_elapsed.avg",
         "smsp__cycles_active.avg", "sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_active",
-        "sm__inst_executed_pipe_lsu.sum", "smsp__sass_thread_inst_executed_op_fadd_pred_on.sum",
-        "smsp__sass_thread_inst_executed_op_fmul_pred_on.sum", "smsp__sass_thread_inst_executed_op_ffma_pred_on.sum"]
+        "launch__shared_mem_per_block_dynamic"]
 
 
-def launches(path):
-    rows = [r for r in csv.reader(l for l in open(path) if l.startswith('"'))]
-    hdr = rows[0]
-    k, v = hdr.index("Kernel Name"), hdr.index("Metric Value")
-    g, b = hdr.index("Grid Size"), hdr.index("Block Size")
-    agg = defaultdict(lambda: [0, 0.0, "", ""])
-    for r in rows[1:]:
-        name = r[k].split("(")[0]
-        a = agg[name]
-        a[0] += 1
-        a[1] += float(r[v].replace(",", ""))
-        a[2], a[3] = r[g], r[b]
-    tot = sum(a[1] for a in agg.values())
-    print("| kernel | launches | grid | block | total ms | share |\n|---|---|---|---|---|---|")
-    for name, a in sorted(agg.items(), key=lambda x: -x[1][1]):
-        print(f"| `{name}` | {a[0]} | {a[2]} | {a[3]} | {a[1] / 1e6:.3f} | {100 * a[1] / tot:.2f} % |")
-    print(f"\ntotal device time in kernels: {tot / 1e6:.3f} ms over {sum(a[0] for a in agg.values())} launches")
+def raw_page(rep):
+    txt = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True, check=True).stdout
+    rows = list(csv.reader(io.StringIO(txt)))
+    header, units, vals = rows[0], rows[1], rows[2]
+    return OrderedDict((h, (v, u)) for h, u, v in zip(header, units, vals))
 
 
-def full(path, steps, cells):
-    out = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
-    rows = list(csv.reader(io.StringIO(out)))
-    hdr, units, vals = rows[0], rows[1], rows[2]
-    d = {h: (vals[i], units[i]) for i, h in enumerate(hdr)}
-    print(f"kernel: `{d['Kernel Name'][0].split('(')[0]}`  grid {d['Grid Size'][0]} block {d['Block Size'][0]}\n")
-    print("| metric | value | unit |\n|---|---|---|")
-    for key in KEEP:
-        if key in d:
-            print(f"| {key} | {d[key][0]} | {d[key][1]} |")
-    stalls = {h: float(v[0]) for h, v in d.items() if h.startswith("smsp__average_warps_issue_stalled") and v[0] not in ("", "n/a")}
-    print("\nwarp stall reasons (warps stalled per issue-active cycle), top 8:\n")
-    for h, v in sorted(stalls.items(), key=lambda x: -x[1])[:8]:
-        print(f"* {h.replace('smsp__average_warps_issue_stalled_', '').replace('_per_issue_active.ratio', '')}: {v:.3f}")
-    def num(key):
-        v, u = d[key]
-        f = float(v.replace(",", ""))
-        return f * {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1, "ms": 1e-3, "us": 1e-6, "ns": 1e-9, "s": 1.0, "second": 1.0,
-                    "msecond": 1e-3, "usecond": 1e-6, "nsecond": 1e-9}.get(u, 1)
-    t = num("gpu__time_duration.sum")
-    dram = num("dram__bytes_read.sum") + num("dram__bytes_write.sum")
+def to_bytes(v, u):
+    f = float(v.replace(",", ""))
+    return f * {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12}[u]
+
+
+def to_ms(v, u):
+    f = float(v.replace(",", ""))
+    return f * {"ns": 1e-6, "us": 1e-3, "ms": 1.0, "s": 1e3, "nsecond": 1e-6, "usecond": 1e-3, "msecond": 1.0, "second": 1e3}[u]
+
+
+def full_summary(tag, grid, steps):
+    rep = os.path.join(OUT, f"prof_persistent_{grid}.ncu-rep")
+    m = raw_page(rep)
+    nx, ny = (int(v) for v in grid.split("x"))
+    cells = nx * ny
+    lines = [f"# {tag} — ncu --set full of lbm_persistent_kernel<strict> on {grid} ({steps} timesteps in one launch)", "",
+             f"Command: `python tools/explore.py --grid {grid} --steps {steps} --reps 1 --configs 1:256:2:1` (2nd launch captured, "
+             f"`-s 1 -c 1`), ncu --set full --clock-control none --import-source on (tools/profile_r01.sh). "
+             f"Report: gpurun_out/prof_persistent_{grid}.ncu-rep (scratch).", "",
+             f"kernel: `{m['Kernel Name'][0]}`  grid {m.get('Grid Size', ('?',))[0]} block {m.get('Block Size', ('?',))[0]}", "",
+             "| metric | value | unit |", "|---|---|---|"]
+    for k in WANT:
+        if k in m:
+            lines.append(f"| {k} | {m[k][0]} | {m[k][1]} |")
+    stalls = sorted(((float(v[0].replace(",", "")), k.split("issue_stalled_")[1].split("_per_warp")[0]) for k, v in m.items()
+                     if k.startswith("smsp__average_warps_issue_stalled_") and k.endswith("_per_issue_active.ratio")),
+                    reverse=True)[:8]
+    if not stalls:
+        stalls = sorted(((float(v[0].replace(",", "")), k.replace("smsp__average_warp_latency_issue_stalled_", "").replace(".ratio", ""))
+                         for k, v in m.items() if k.startswith("smsp__average_warp_latency_issue_stalled_")), reverse=True)[:8]
+    lines += ["", "warp stall reasons (warps stalled per issue-active cycle), top 8:", ""]
+    lines += [f"* {n}: {v:.3f}" for v, n in stalls]
+    ms = to_ms(*m["gpu__time_duration.sum"])
+    rd, wr = to_bytes(*m["dram__bytes_read.sum"]), to_bytes(*m["dram__bytes_write.sum"])
     alg = 72.0 * steps * cells
-    inst = float(d["smsp__inst_executed.sum"][0].replace(",", ""))
-    print(f"\nderived: launch = {steps} timesteps x {cells} cells; duration under ncu {t * 1e3:.3f} ms "
-          f"({t / steps * 1e6:.2f} us/step, cold caches, serialised)")
-    print(f"* algorithmic bytes per launch = 72 x {steps} x {cells} = {alg / 1e9:.3f} GB -> {alg / t / 1e9:.0f} GB/s under ncu")
-    print(f"* DRAM traffic per launch (dram__bytes_read+write) = {dram / 1e9:.3f} GB = {dram / alg:.3f} x algorithmic "
-          f"({dram / steps / cells:.1f} B per cell update)")
-    print(f"* warp instructions per 128-cell task = {inst / (steps * cells / 128):.0f}  ({inst / (steps * cells) * 32 / 32:.2f} per cell per lane-quad x4)")
+    inst = float(m["smsp__inst_executed.sum"][0].replace(",", ""))
+    tasks = steps * ny * ((nx + 127) // 128)
+    lines += ["", f"derived: launch = {steps} timesteps x {cells} cells; duration under ncu {ms:.3f} ms "
+                  f"({ms / steps * 1e3:.2f} us/step, cold caches, serialised)",
+              f"* algorithmic bytes per launch = 72 x {steps} x {cells} = {alg / 1e9:.3f} GB -> {alg / ms / 1e6:.0f} GB/s under ncu",
+              f"* DRAM traffic per launch (dram__bytes_read+write) = {(rd + wr) / 1e9:.3f} GB = {(rd + wr) / alg:.3f} x algorithmic "
+              f"({(rd + wr) / (steps * cells):.1f} B per cell update)",
+              f"* warp instructions per 128-cell task = {inst / tasks:.0f}  ({inst / tasks / 128:.2f} per cell per lane-quad x4)"]
+    with open(os.path.join(PROF, f"{tag}_ncu_persistent_{grid}.md"), "w") as fh:
+        fh.write("\n".join(lines) + "\n")
+    return (rd + wr) / (steps * cells)
+
+
+def launch_list(tag):
+    src = os.path.join(OUT, "launches_bench.csv")
+    rows = []
+    with open(src) as fh:
+        txt = [l for l in fh if not l.startswith("==")]
+    for r in csv.DictReader(io.StringIO("".join(txt))):
+        if r.get("Metric Name") == "gpu__time_duration.sum":
+            ms = to_ms(r["Metric Value"], r["Metric Unit"])
+            rows.append((r["Kernel Name"], r["Grid Size"], r["Block Size"], ms))
+    agg = OrderedDict()
+    for name, g, b, ms in rows:
+        key = (name, g, b)
+        n, t = agg.get(key, (0, 0.0))
+        agg[key] = (n + 1, t + ms)
+    tot = sum(t for _, t in agg.values())
+    lines = [f"# {tag} — launch list of `python bench.py --steps 1 --warmup 3 --iters 300 --no-cpu-baseline`", "",
+             f"ncu --metrics gpu__time_duration.sum --clock-control none (cold-cache, serialised: compare SHARES). "
+             f"Raw CSV: {tag}_launches_bench.csv", "", "| kernel | launches | grid | block | total ms | share |", "|---|---|---|---|---|---|"]
+    for (name, g, b), (n, t) in sorted(agg.items(), key=lambda kv: -kv[1][1]):
+        lines.append(f"| `{name[:110]}` | {n} | {g} | {b} | {t:.3f} | {100 * t / tot:.2f} % |")
+    lines += ["", f"total device time in kernels: {tot:.3f} ms over {len(rows)} launches", "",
+              "The timestep kernel (one persistent launch per lbm_run) is the only kernel that matters in a bench run;",
+              "k_fill_uniform = initial state, k_fold_partials = av_vels fold, the at:: kernels are bench.py's L2 flush."]
+    with open(os.path.join(PROF, f"{tag}_launches.md"), "w") as fh:
+        fh.write("\n".join(lines) + "\n")
+    with open(os.path.join(PROF, f"{tag}_launches_bench.csv"), "w") as fh:
+        fh.write("".join(txt))
+
+
+def main():
+    tag = sys.argv[1] if len(sys.argv) > 1 else "r01"
+    launch_list(tag)
+    per = {}
+    for grid, steps in (("16384x1024", 40), ("1024x1024", 300)):
+        per[grid] = round(full_summary(tag, grid, steps), 2)
+    with open(os.path.join(PROF, "traffic.json"), "w") as fh:
+        json.dump({"source": "ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum of one lbm_persistent_kernel launch / "
+                             f"(timesteps x cells) - see profiles/{tag}_ncu_persistent_<grid>.md",
+                   "dram_bytes_per_cell_update": per}, fh, indent=1)
+        fh.write("\n")
+    print(per)
 
 
 if __name__ == "__main__":
-    if sys.argv[1] == "launches":
-        launches(sys.argv[2])
-    else:
-        full(sys.argv[2], int(sys.argv[3]), int(sys.argv[4]))
+    main()
