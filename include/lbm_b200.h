@@ -166,7 +166,7 @@ int lbm_selftest_math(long long n, long long seed, long long* mismatches);
 
 /* ---- one process per GPU (torchrun-style launch) -------------------------------
  * Rank r of `size` owns slab r on CUDA device `device`.  After creation every rank
- * exports an opaque blob (CUDA IPC handles of its halo rows and progress flags), the
+ * exports an opaque blob (the CUDA IPC handle of its inbound halo slots), the
  * host program exchanges blobs with the ring neighbours by whatever transport it has
  * (torch.distributed, MPI, files), and lbm_rank_connect maps them.  lbm_run/lbm_sync/
  * lbm_get_* then act on the local slab only: lbm_get_av_vels returns this rank's
