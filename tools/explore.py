@@ -10,6 +10,15 @@ sys.path.insert(0, ROOT)
 lbm = importlib.import_module("lattice-boltzmann_b200")
 
 
+def hbm_gbs():
+    import json
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as fh:
+            return float(json.load(fh)["hbm_gbs"])
+    except Exception:
+        return 6650.0
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--grid", default="1024x1024")
@@ -51,7 +60,7 @@ def main():
             best = min(best, lat.last_run_ms())
         glups = cells * args.steps / (best * 1e-3) / 1e9
         print(f"{args.grid} cfg={cfg} [{lat.describe()}] {best / args.steps * 1e3:.2f} us/step  {glups:.2f} GLUPS  "
-              f"{glups * 72 / 6456.2 * 100 / args.ngpus:.1f}% of measured HBM roofline", flush=True)
+              f"{glups * 72 / hbm_gbs() * 100 / args.ngpus:.1f}% of measured HBM roofline", flush=True)
         lat.close()
 
 
