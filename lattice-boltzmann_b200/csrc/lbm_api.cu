@@ -338,14 +338,14 @@ int slab_create(lbm_ctx* c, Slab& s, int rank, int device, const int* obst)
     CK(cudaMemsetAsync(s.step_ptr, 0, sizeof(int), s.stream));
 
     // schedule arrays, one allocation: task_order as (row, chunk) pairs first (8-byte aligned), then
-    // task_begin | n_interior | dep_begin | deps
+    // task_begin | n_interior | n_edge | dep_begin | deps
     std::vector<int> h;
     auto put = [&h](const std::vector<int>& v) { size_t o = h.size(); h.insert(h.end(), v.begin(), v.end()); return o; };
     std::vector<int> pairs;
     pairs.reserve(2 * pl.task_order.size());
     for (int t : pl.task_order) { pairs.push_back(t / pl.tpr); pairs.push_back(t % pl.tpr); }
     const size_t o_to = put(pairs);
-    const size_t o_tb = put(pl.task_begin), o_ni = put(pl.n_interior),
+    const size_t o_tb = put(pl.task_begin), o_ni = put(pl.n_interior), o_ne = put(pl.n_edge),
                  o_db = put(pl.dep_begin), o_dp = put(pl.deps);
     h.push_back(0);
     CK(cudaMalloc(&s.sched, sizeof(int) * h.size()));
@@ -371,7 +371,7 @@ int slab_create(lbm_ctx* c, Slab& s, int rank, int device, const int* obst)
     d.aw1 = P.density * P.accel / 9.f;       // d2q9-bgk.c:237
     d.aw2 = P.density * P.accel / 36.f;      // d2q9-bgk.c:238
     d.ll_in = s.ll_in; d.ll_up = d.ll_down = nullptr;
-    d.task_begin = s.sched + o_tb; d.n_interior = s.sched + o_ni; d.task_order = (const int2*)(s.sched + o_to);
+    d.task_begin = s.sched + o_tb; d.n_interior = s.sched + o_ni; d.n_edge = s.sched + o_ne; d.task_order = (const int2*)(s.sched + o_to);
     d.dep_begin = s.sched + o_db; d.deps = s.sched + o_dp;
     d.flags = s.flags;
     d.num_ctas = G;

@@ -364,6 +364,7 @@ __global__ void __launch_bounds__(512, 1) lbm_persistent_kernel(SlabDev d, int p
     const int b = blockIdx.x;
     const int t_lo = __ldg(d.task_begin + b), t_hi = __ldg(d.task_begin + b + 1);
     const int n_int = __ldg(d.n_interior + b);
+    const int edge_end = RING ? n_int + __ldg(d.n_edge + b) : n_int;
     const int dep_lo = __ldg(d.dep_begin + b), dep_hi = __ldg(d.dep_begin + b + 1);
     const int n_tasks = t_hi - t_lo;
     // edge tasks are staged one task ahead; a one-row slab needs both sides at once and just polls
@@ -395,12 +396,10 @@ __global__ void __launch_bounds__(512, 1) lbm_persistent_kernel(SlabDev d, int p
         for (int k = warp; k < n_tasks; k += nw, ++ord) {
             bool staged_next = false;
             if (staging) {
-                if (k + nw < n_tasks) {
-                    const int2 tn = __ldg(d.task_order + t_lo + k + nw);
-                    if (tn.x == 0 || tn.x == d.rows - 1) {
-                        ll_prefetch(d, par, tn, lane, my_stage + ((ord + 1) & 1) * kStageRecords);
-                        staged_next = true;
-                    }
+                const int kn = k + nw;           // edge tasks sit at [n_int, edge_end) of the CTA's list
+                if (kn >= n_int && kn < edge_end) {
+                    ll_prefetch(d, par, __ldg(d.task_order + t_lo + kn), lane, my_stage + ((ord + 1) & 1) * kStageRecords);
+                    staged_next = true;
                 }
                 cp_async_commit();               // one group per task, empty or not
             }

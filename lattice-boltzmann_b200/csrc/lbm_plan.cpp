@@ -144,6 +144,7 @@ SlabPlan make_plan(int nx, int ny, int rank, int size, int ctas)
 
     p.task_begin.assign(G + 1, 0);
     p.n_interior.assign(G, 0);
+    p.n_edge.assign(G, 0);
     p.dep_begin.assign(G + 1, 0);
     p.task_order.reserve(T);
 
@@ -171,6 +172,7 @@ SlabPlan make_plan(int nx, int ny, int rank, int size, int ctas)
             (inside ? interior : is_edge ? edge : boundary).push_back(lr * p.tpr + ch);
         }
         p.n_interior[b] = (int)interior.size();
+        p.n_edge[b] = (int)edge.size();
         p.task_order.insert(p.task_order.end(), interior.begin(), interior.end());
         p.task_order.insert(p.task_order.end(), edge.begin(), edge.end());
         p.task_order.insert(p.task_order.end(), boundary.begin(), boundary.end());
@@ -204,6 +206,8 @@ std::string validate_plan(const SlabPlan& p)
             const bool is_edge = p.size > 1 && (lr == 0 || lr == p.rows - 1);
             if (is_edge && is_int) return "edge task scheduled as interior";
             if (is_edge && seen_plain) return "edge tasks must lead the boundary tasks";
+            const int rel = k - p.task_begin[b] - p.n_interior[b];
+            if (is_edge != (rel >= 0 && rel < p.n_edge[b])) return "n_edge does not delimit the edge tasks";
             seen_plain = seen_plain || (!is_int && !is_edge);
             bool all_mine = true;
             for (int dy = -1; dy <= 1; ++dy)

@@ -70,6 +70,7 @@ struct SlabPlan {
     // schedule (CSR style)
     std::vector<int> task_begin;   // G+1 offsets into task_order
     std::vector<int> n_interior;   // G: the first n_interior[b] tasks of CTA b are interior
+    std::vector<int> n_edge;       // G: the next n_edge[b] tasks are slab-edge tasks (0 on a single lattice)
     std::vector<int> task_order;   // num_tasks flat task ids; per CTA: interior, edge, boundary
     std::vector<int> dep_begin;    // G+1 offsets into deps
     std::vector<int> deps;         // CTAs (flag indices) a CTA's boundary tasks wait for
