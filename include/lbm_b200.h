@@ -98,6 +98,11 @@ int lbm_sync(lbm_ctx* ctx);
  * n <= steps_done.  Synchronises. */
 int lbm_get_av_vels(lbm_ctx* ctx, float* out, int n);
 
+/* The un-normalised per-step sums of |u| over fluid cells (what timestep() returns and the
+ * reference's -DDEBUG build prints as "av velocity", d2q9-bgk.c:193,200) for steps
+ * [first, first + n), summed over this context's slabs.  first + n <= steps_done.  Synchronises. */
+int lbm_get_tot_u(lbm_ctx* ctx, float* out, int first, int n);
+
 /* Gathers every slab's rows into nine global planes of ny*nx floats (:397-443; the
  * result is what the reference holds in cells_global).  Synchronises. */
 int lbm_get_cells(lbm_ctx* ctx, float* const speeds[LBM_NSPEEDS]);

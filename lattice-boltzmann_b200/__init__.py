@@ -50,6 +50,7 @@ SYMBOLS = {
     "lbm_run": (ctypes.c_int, [_P, ctypes.c_int]),
     "lbm_sync": (ctypes.c_int, [_P]),
     "lbm_get_av_vels": (ctypes.c_int, [_P, _P, ctypes.c_int]),
+    "lbm_get_tot_u": (ctypes.c_int, [_P, _P, ctypes.c_int, ctypes.c_int]),
     "lbm_get_cells": (ctypes.c_int, [_P, ctypes.POINTER(_P)]),
     "lbm_set_cells": (ctypes.c_int, [_P, ctypes.POINTER(_P)]),
     "lbm_get_final_state": (ctypes.c_int, [_P, _P, _P, _P, _P]),
@@ -193,6 +194,13 @@ class Lattice:
         n = self.steps_done if n is None else n
         out = np.empty(n, np.float32)
         self._ck(self.lib.lbm_get_av_vels(self._ctx, out.ctypes.data, n))
+        return out
+
+    def tot_u(self, first=0, n=None):
+        """Un-normalised per-step sums of |u| (timestep()'s return value, d2q9-bgk.c:193) for steps [first, first+n)."""
+        n = self.steps_done - first if n is None else n
+        out = np.empty(n, np.float32)
+        self._ck(self.lib.lbm_get_tot_u(self._ctx, out.ctypes.data, first, n))
         return out
 
     def cells(self):

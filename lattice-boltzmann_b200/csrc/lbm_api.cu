@@ -727,25 +727,45 @@ int fold_partials(lbm_ctx* c, Slab& s)
 
 extern "C" {
 
-int lbm_get_av_vels(lbm_ctx* c, float* out, int n)
+// Sum over this context's slabs of the per-step sums of |u| for steps [first, first + n), in double.
+static int gather_tot_u(lbm_ctx* c, int first, int n, std::vector<double>& sum)
 {
-    if (!c || !out) return fail("bad arguments");
-    if (n < 0 || n > c->steps_done) return fail("lbm_get_av_vels: n=%d but only %d steps done", n, c->steps_done);
     if (lbm_sync(c)) return 1;
-    std::vector<double> sum((size_t)n, 0.0), tmp((size_t)n);
+    sum.assign((size_t)n, 0.0);
+    std::vector<double> tmp((size_t)n);
     for (Slab& s : c->slabs) {
         if (fold_partials(c, s)) return 1;
-        CK(cudaMemcpyAsync(tmp.data(), s.tot, sizeof(double) * n, cudaMemcpyDeviceToHost, s.stream));
+        CK(cudaMemcpyAsync(tmp.data(), s.tot + first, sizeof(double) * n, cudaMemcpyDeviceToHost, s.stream));
         c->d2h_bytes += (long long)sizeof(double) * n;
         CK(cudaStreamSynchronize(s.stream));
         for (int t = 0; t < n; ++t) sum[t] += tmp[t];           // the one reduction over slabs (:445)
     }
+    return 0;
+}
+
+int lbm_get_av_vels(lbm_ctx* c, float* out, int n)
+{
+    if (!c || !out) return fail("bad arguments");
+    if (n < 0 || n > c->steps_done) return fail("lbm_get_av_vels: n=%d but only %d steps done", n, c->steps_done);
+    std::vector<double> sum;
+    if (gather_tot_u(c, 0, n, sum)) return 1;
     if (c->rank_mode) {   // un-normalised local partial; the caller sums across ranks, then scales
         for (int t = 0; t < n; ++t) out[t] = (float)sum[t];
     } else {
         const float r = 1.f / (float)c->free_cells;              // :642
         for (int t = 0; t < n; ++t) out[t] = (float)sum[t] * r;  // :446
     }
+    return 0;
+}
+
+int lbm_get_tot_u(lbm_ctx* c, float* out, int first, int n)
+{
+    if (!c || !out) return fail("bad arguments");
+    if (first < 0 || n < 0 || first + n > c->steps_done)
+        return fail("lbm_get_tot_u: steps [%d,%d) requested but only %d done", first, first + n, c->steps_done);
+    std::vector<double> sum;
+    if (gather_tot_u(c, first, n, sum)) return 1;
+    for (int t = 0; t < n; ++t) out[t] = (float)sum[t];
     return 0;
 }
 

@@ -7,6 +7,7 @@
 #   ref-omp    : the reference's OpenMP variant = the same file with its three
 #                commented-out "#pragma omp parallel for" lines (d2q9-bgk.c:278,588,607)
 #                re-enabled on the fly by sed, + -fopenmp (reference Makefile:7)
+#   ref-debug  : ref-serial with -DDEBUG (per-step "av velocity" / "tot density" lines, :198-202)
 #
 # The source is read where it lies under $REF (default /root/reference); no copy of
 # it is written anywhere (the sed output is piped straight into gcc).  Outputs go
@@ -25,6 +26,7 @@ mkdir -p "$out"
 DEFS=(-D'__assume(x)=((void)0)' -D'__assume_aligned(p,a)=((void)0)')
 CFLAGS=(-std=gnu99 -O3 -I"$here/mpi_stub" -w)
 gcc "${CFLAGS[@]}" "${DEFS[@]}" "$src" -lm -o "$out/ref-serial"
+gcc "${CFLAGS[@]}" "${DEFS[@]}" -DDEBUG "$src" -lm -o "$out/ref-debug"
 sed 's#^\( *\)// \#pragma omp parallel for#\1\#pragma omp parallel for#' "$src" \
   | gcc "${CFLAGS[@]}" "${DEFS[@]}" -fopenmp -x c - -lm -o "$out/ref-omp"
-echo "built $out/ref-serial $out/ref-omp"
+echo "built $out/ref-serial $out/ref-omp $out/ref-debug"

@@ -15,6 +15,9 @@
  *   LBM_TRUE_FREE_CELLS=1  divide av_vels by the true number of free cells instead of the
  *                  reference's nx*ny - <obstacle file lines> (:626,640,642)
  *   LBM_REPORT=1   print GLUPS / roofline lines on stderr (stdout stays byte-compatible)
+ *   LBM_DEBUG=1    the reference's -DDEBUG build (:198-202; also selected by compiling this file with
+ *                  -DDEBUG): one timestep per launch, printing "==timestep: t==", the step's
+ *                  un-normalised sum of |u| and the total density (the conservation invariant)
  */
 #include <math.h>
 #include <stdio.h>
@@ -193,7 +196,25 @@ int main(int argc, char* argv[])
     /* Init time stops here, compute time starts */
     const double init_toc = wall(), comp_tic = init_toc;
 
-    LBM_OK(lbm_run(ctx, p.max_iters));   /* the whole time loop, enqueued once: no per-step host work */
+    int debug = 0;
+#ifdef DEBUG
+    debug = 1;
+#endif
+    const char* dbg = getenv("LBM_DEBUG");
+    if (dbg && atoi(dbg)) debug = 1;
+    if (!debug) {
+        LBM_OK(lbm_run(ctx, p.max_iters));   /* the whole time loop, enqueued once: no per-step host work */
+    } else {
+        for (int tt = 0; tt < p.max_iters; tt++) {   /* the reference's DEBUG loop body (:198-202) */
+            float tot_u = 0.f, density = 0.f;
+            LBM_OK(lbm_run(ctx, 1));
+            LBM_OK(lbm_get_tot_u(ctx, &tot_u, tt, 1));
+            LBM_OK(lbm_total_density(ctx, &density));
+            printf("==timestep: %d==\n", tt);
+            printf("av velocity: %.12E\n", tot_u);
+            printf("tot density: %.12E\n", density);
+        }
+    }
     LBM_OK(lbm_sync(ctx));
 
     /* Compute time stops here, collate time starts */

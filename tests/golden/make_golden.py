@@ -8,6 +8,7 @@ Nothing here runs on the GPU box; the .npz files it writes are committed.
                          (the columns check/check.py:60-61 reads: av_vels col 1, final_state
                          cols 0,1,5), stored as float64 exactly as np.loadtxt parses them (the shipped
                          values are not fp32-representable: they came from a different build).
+  ref_debug_<g>_<n>.txt  the per-step lines printed by the reference built with -DDEBUG (ref-debug)
   ref_full_<g>.npz       outputs of the UNMODIFIED reference (ref-serial, gcc -O3) on the shipped
                          inputs at full length: av_vels, u_x, u_y, |u|, pressure, Reynolds line.
                          Fills the two final_state goldens missing from the reference mount
@@ -36,6 +37,9 @@ SHIPPED = {"128x128": True, "128x256": True, "256x256": False, "1024x1024": Fals
 SHORT = {"128x128": 1000, "128x256": 1000, "256x256": 1000, "1024x1024": 200, "2048x1024": 100}
 
 
+DEBUG_CASE = ("128x256", 25)
+
+
 def load_av(path):
     return np.loadtxt(path, usecols=[1])
 
@@ -62,8 +66,8 @@ def shipped():
         print("wrote shipped", g, {k: v.shape for k, v in out.items()})
 
 
-def run_ref(g, iters, workdir):
-    """Runs ref-serial on grid g (maxIters overridden if iters) inside workdir."""
+def run_ref(g, iters, workdir, binary=None):
+    """Runs ref-serial (or `binary`) on grid g (maxIters overridden if iters) inside workdir."""
     with open(os.path.join(ROOT, "inputs", f"input_{g}.params")) as fh:
         lines = fh.read().split("\n")
     if iters:
@@ -71,7 +75,7 @@ def run_ref(g, iters, workdir):
     pfile = os.path.join(workdir, "in.params")
     with open(pfile, "w") as fh:
         fh.write("\n".join(lines))
-    res = subprocess.run([REF_BIN, pfile, os.path.join(ROOT, "inputs", f"obstacles_{g}.dat")],
+    res = subprocess.run([binary or REF_BIN, pfile, os.path.join(ROOT, "inputs", f"obstacles_{g}.dat")],
                          cwd=workdir, check=True, capture_output=True, text=True)
     with open(os.path.join(workdir, "stdout.txt"), "w") as fh:
         fh.write(res.stdout)
@@ -118,6 +122,15 @@ def main():
             out = collect(g, tmp, fields)
         np.savez_compressed(os.path.join(HERE, f"ref_short_{g}_{n}.npz"), **out)
         print("wrote ref_short", g, n)
+    # the reference's -DDEBUG build (d2q9-bgk.c:198-202): per-step "av velocity" / "tot density" lines
+    g, n = DEBUG_CASE
+    with tempfile.TemporaryDirectory() as tmp:
+        run_ref(g, n, tmp, os.path.join(ROOT, "oracle", "_ref", "ref-debug"))
+        with open(os.path.join(tmp, "stdout.txt")) as fh:
+            dbg = [l for l in fh.read().splitlines(True) if re.match(r"==timestep|av velocity|tot density", l)]
+    with open(os.path.join(HERE, f"ref_debug_{g}_{n}.txt"), "w") as fh:
+        fh.writelines(dbg)
+    print("wrote ref_debug", g, n, len(dbg), "lines")
     return 0
 
 

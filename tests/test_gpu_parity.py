@@ -165,6 +165,47 @@ def test_cli_end_to_end_judged_by_checker(lbm, golden, tmp_path):
     assert c.returncode == 0 and "Both tests passed!" in c.stdout, c.stdout
 
 
+def test_cli_debug_mode_matches_reference_debug_build(lbm, tmp_path):
+    """LBM_DEBUG=1 ./d2q9-bgk = the reference compiled with -DDEBUG (d2q9-bgk.c:198-202): per step the
+    un-normalised sum of |u| (timestep()'s return value) and the total density.  Fixture: the unmodified
+    reference's own DEBUG output (tests/golden/make_golden.py).  Tolerances: the reference accumulates both
+    sequentially in fp32 - 1e-4 on |u| over 32k cells; its density sum over 295k values is off the exact
+    mass by 8e-4, ours (double tree sum) must match the exact mass to 1e-6 and the reference to 2e-3."""
+    import os, re, subprocess
+    import oracle_lib
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    steps = 25
+    pfile, ofile = oracle_lib.grid_files("128x256")
+    lines = open(pfile).read().split("\n")
+    lines[2] = str(steps)
+    (tmp_path / "p.params").write_text("\n".join(lines))
+    r = subprocess.run([os.path.join(root, "d2q9-bgk"), str(tmp_path / "p.params"), ofile], cwd=tmp_path,
+                       capture_output=True, text=True, timeout=300, env=dict(os.environ, LBM_DEBUG="1"))
+    assert r.returncode == 0, r.stderr
+    got = [l for l in r.stdout.splitlines() if re.match(r"==timestep|av velocity|tot density", l)]
+    ref = open(os.path.join(root, "tests", "golden", f"ref_debug_128x256_{steps}.txt")).read().splitlines()
+    assert len(got) == len(ref) == 3 * steps
+    mass = 0.1 * 128 * 256
+    for a, b in zip(got, ref):
+        if a.startswith("=="):
+            assert a == b
+            continue
+        ka, va = a.split(": ")
+        kb, vb = b.split(": ")
+        assert ka == kb and re.fullmatch(r"\d\.\d{12}E[+-]\d\d", va)
+        if ka == "av velocity":
+            assert abs(float(va) - float(vb)) <= AV_RTOL * float(vb)
+        else:
+            assert abs(float(va) - mass) <= 1e-6 * mass and abs(float(va) - float(vb)) <= 2e-3 * float(vb)
+    assert r.stdout.splitlines()[3 * steps] == "==done=="
+    # the normalised record of the same run equals tot_u / free cells (collate, :446)
+    p, mask, nlines = load_grid("128x256")
+    with make(lbm, p, mask, nlines, iters=steps) as lat:
+        lat.run(steps)
+        np.testing.assert_array_equal(lat.av_vels(), lat.tot_u() * lat.inv_free_cells())
+        assert lat.tot_u(first=7, n=3).tolist() == lat.tot_u()[7:10].tolist()
+
+
 @pytest.mark.parametrize("seed", [1, 2026, 99991])
 def test_exact_division_and_sqrt_fast_paths(lbm, seed):
     """The shared-reciprocal division and the rsqrt-based root used inside the kernel are bit-identical
