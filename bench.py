@@ -313,7 +313,7 @@ def main():
     torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", "0")))
     if world > 1:
         import torch.distributed as dist
-        os.environ["NCCL_DEBUG"] = "WARN"                # keep NCCL's version banner off stdout (one JSON line only)
+        os.environ.pop("NCCL_DEBUG", None)               # VERSION/WARN/INFO all print a banner on stdout; the bench prints one JSON line
         dist.init_process_group("nccl", device_id=torch.device("cuda", torch.cuda.current_device()))
     if world != args.gpus:
         raise SystemExit(f"bench.py: --gpus {args.gpus} needs {args.gpus} ranks (torchrun), got WORLD_SIZE={world}")
