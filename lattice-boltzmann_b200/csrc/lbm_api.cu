@@ -228,10 +228,19 @@ __global__ void k_selftest_math(unsigned long long n, unsigned long long seed, i
 // =========================================================================== slab set-up
 namespace {
 
+int env_int(const char* name, int dflt);
+
+template <bool PROF>
+const void* persistent_pick(bool strict, bool ring)
+{
+    if (ring) return strict ? (const void*)lbm::lbm_persistent_kernel<true, true, PROF> : (const void*)lbm::lbm_persistent_kernel<false, true, PROF>;
+    return strict ? (const void*)lbm::lbm_persistent_kernel<true, false, PROF> : (const void*)lbm::lbm_persistent_kernel<false, false, PROF>;
+}
+
+// LBM_PROFILE=1 selects the instantiations that carry the per-warp cycle counters
 const void* persistent_fn(bool strict, bool ring)
 {
-    if (ring) return strict ? (const void*)lbm::lbm_persistent_kernel<true, true> : (const void*)lbm::lbm_persistent_kernel<false, true>;
-    return strict ? (const void*)lbm::lbm_persistent_kernel<true, false> : (const void*)lbm::lbm_persistent_kernel<false, false>;
+    return env_int("LBM_PROFILE", 0) ? persistent_pick<true>(strict, ring) : persistent_pick<false>(strict, ring);
 }
 
 int env_int(const char* name, int dflt)

@@ -74,29 +74,45 @@ __device__ __forceinline__ void ll_addresses(const SlabDev& d, const uint4* base
 // slots, spinning until every record carries `tag`.  SIDE 0: row below (f2,f5,f6: west element is
 // f5 = b3 of the group before, east element f6 = c0 of the group after); SIDE 1: row above
 // (f4,f7,f8: west element f8 = c3, east element f7 = b0).  Warp-uniform: all 32 lanes call it.
+// Only taken when the staged copy (ll_take) was not there or not complete yet, so it is kept OUT OF
+// LINE: the persistent kernel's steady-state code must stay inside the 32 KB instruction cache.
+struct HaloRow { float4 v0, v1, v2; float w, e; };
+
 template <int SIDE>
-__device__ __forceinline__ void ll_pull(const SlabDev& d, const uint4* base, const TaskGeom& g, unsigned tag,
-                                        float4 (&v)[3], float& w, float& e)
+__device__ __noinline__ HaloRow ll_pull_slow(const uint4* pq, const uint4* pw, const uint4* pe, int Q, bool need_w, bool need_e,
+                                             unsigned tag, int* status)
 {
-    const int Q = d.nx >> 2;
-    const uint4 *pq, *pw, *pe;
-    ll_addresses<SIDE>(d, base, g, pq, pw, pe);
+    HaloRow h;
+    h.w = 0.f; h.e = 0.f;
     const long long t0 = clock64();
     for (;;) {
         const uint4 r0 = ld_record(pq), r1 = ld_record(pq + Q), r2 = ld_record(pq + 2 * Q), r3 = ld_record(pq + 3 * Q);
         bool ok = r0.w == tag && r1.w == tag && r2.w == tag && r3.w == tag;
-        v[0] = make_float4(__uint_as_float(r0.x), __uint_as_float(r0.y), __uint_as_float(r0.z), __uint_as_float(r1.x));
-        v[1] = make_float4(__uint_as_float(r1.y), __uint_as_float(r1.z), __uint_as_float(r2.x), __uint_as_float(r2.y));
-        v[2] = make_float4(__uint_as_float(r2.z), __uint_as_float(r3.x), __uint_as_float(r3.y), __uint_as_float(r3.z));
-        if (g.need_w) { const uint4 q = ld_record(pw); ok = ok && q.w == tag; w = __uint_as_float(SIDE ? q.z : q.y); }
-        if (g.need_e) { const uint4 q = ld_record(pe); ok = ok && q.w == tag; e = __uint_as_float(SIDE ? q.y : q.z); }
+        h.v0 = make_float4(__uint_as_float(r0.x), __uint_as_float(r0.y), __uint_as_float(r0.z), __uint_as_float(r1.x));
+        h.v1 = make_float4(__uint_as_float(r1.y), __uint_as_float(r1.z), __uint_as_float(r2.x), __uint_as_float(r2.y));
+        h.v2 = make_float4(__uint_as_float(r2.z), __uint_as_float(r3.x), __uint_as_float(r3.y), __uint_as_float(r3.z));
+        if (need_w) { const uint4 q = ld_record(pw); ok = ok && q.w == tag; h.w = __uint_as_float(SIDE ? q.z : q.y); }
+        if (need_e) { const uint4 q = ld_record(pe); ok = ok && q.w == tag; h.e = __uint_as_float(SIDE ? q.y : q.z); }
         if (__all_sync(0xffffffffu, ok)) break;
         // give up warp-uniformly (another CTA failed, or the neighbour never arrives)
         const bool late = clock64() - t0 > kSpinLimitCycles;
-        if (late) atomicExch(d.status, 2);
-        if (__any_sync(0xffffffffu, late || *(volatile int*)d.status != 0)) break;
+        if (late) atomicExch(status, 2);
+        if (__any_sync(0xffffffffu, late || *(volatile int*)status != 0)) break;
         __nanosleep(40);
     }
+    return h;
+}
+
+template <int SIDE>
+__device__ __forceinline__ void ll_pull(const SlabDev& d, const uint4* base, const TaskGeom& g, unsigned tag,
+                                        float4 (&v)[3], float& w, float& e)
+{
+    const uint4 *pq, *pw, *pe;
+    ll_addresses<SIDE>(d, base, g, pq, pw, pe);
+    const HaloRow h = ll_pull_slow<SIDE>(pq, pw, pe, d.nx >> 2, g.need_w, g.need_e, tag, d.status);
+    v[0] = h.v0; v[1] = h.v1; v[2] = h.v2;
+    if (g.need_w) w = h.w;
+    if (g.need_e) e = h.e;
 }
 
 // Starts the asynchronous fetch of one edge task's halo records into a shared-memory stage buffer
@@ -355,7 +371,7 @@ __device__ __forceinline__ void wait_deps(const SlabDev& d, int dep_lo, int dep_
     __syncwarp();
 }
 
-template <bool S, bool RING>
+template <bool S, bool RING, bool PROF>
 __global__ void __launch_bounds__(512, 1) lbm_persistent_kernel(SlabDev d, int par0, int step0, int iters, unsigned base)
 {
     __shared__ double red[2][kMaxWarps];
@@ -368,9 +384,10 @@ __global__ void __launch_bounds__(512, 1) lbm_persistent_kernel(SlabDev d, int p
     const int dep_lo = __ldg(d.dep_begin + b), dep_hi = __ldg(d.dep_begin + b + 1);
     const int n_tasks = t_hi - t_lo;
     // edge tasks are staged one task ahead; a one-row slab needs both sides at once and just polls
-    const bool staging = RING && d.rows > 1;
+    // (only the CTAs that own edge tasks carry the staging bookkeeping through their task loop)
+    const bool staging = RING && d.rows > 1 && edge_end > n_int;
     uint4* const my_stage = ll_stage + warp * 2 * kStageRecords;
-    const bool prof = d.prof != nullptr;
+    constexpr bool prof = PROF;               // LBM_PROFILE=1 runs the instantiation with cycle counters
     long long c_wait = 0, c_bar = 0, c_ll = 0;
     const long long c_begin = prof ? clock64() : 0;
 
