@@ -11,7 +11,8 @@ A/B working set, i.e. the honest HBM-bound case), row-decomposed over the N GPUs
 three-population one-row halos pushed over NVLink peer memory from inside the kernel.  One
 workload for all N keeps the driver's scaling efficiency meaningful.  At N = 1 the line also
 carries BASELINE.json's single-GPU roofline headline, 1024x1024, under "also" (75 MB A/B set:
-L2-resident inside a step, so it can exceed the HBM roofline).
+L2-resident inside a step, so it can exceed the HBM roofline); at N = 2 and N = 4 it carries the
+weak-scaling configurations 4096x1024 and 8192x1024 the same way.
 value   = lattice updates of all ranks / device time (CUDA events on the launching stream, max
           over ranks), in GLUPS.
 e2e     = the same metric through the public C ABI with HOST buffers: lbm_create (mask +
@@ -324,16 +325,19 @@ def main():
     res = time_resident(lbm, torch, grid, iters, args.steps, args.warmup, rank, world, dist, scratch)
     e2e = time_e2e(lbm, torch, grid, iters, max(1, min(args.steps, 3)), rank, world, dist)
     also = None
-    if world == 1 and not args.workload:
-        head = "1024x1024"
+    # BASELINE.json's other measured configurations: the single-GPU roofline headline at N = 1, the
+    # weak-scaling pair (2.1 M cells per GPU, as 16384x1024 at 8) at N = 2 and N = 4
+    head = {1: "1024x1024", 2: "4096x1024", 4: "8192x1024"}.get(world)
+    if head and not args.workload:
         hi = lbm.read_params(grid_files(head)[0])["max_iters"]
         r2 = time_resident(lbm, torch, head, hi, max(3, args.steps), 3, rank, world, dist, scratch)
         e2 = time_e2e(lbm, torch, head, hi, 3, rank, world, dist)
+        note = ("BASELINE.json's single-GPU roofline headline; 75 MB A/B set is L2-resident inside a step, so the algorithmic "
+                "rate may exceed the HBM roofline (ncu: 21 B of DRAM traffic per update)") if world == 1 else \
+               "BASELINE.json's weak-scaling configuration for this GPU count (2.1 M cells per GPU)"
         also = {head: {"value": r2["glups"], "unit": "GLUPS", "iters_per_step": hi, "steps": max(3, args.steps),
-                       "ms_per_step": r2["ms_per_step"], "roofline_frac": r2["glups"] * BYTES_PER_UPDATE / hbm_peak()[0],
-                       "e2e": e2["glups"], "gpu_launches": r2["launches"],
-                       "note": "BASELINE.json's single-GPU roofline headline; 75 MB A/B set is L2-resident inside a step, "
-                               "so the algorithmic rate may exceed the HBM roofline (ncu: 21 B of DRAM traffic per update)"}}
+                       "ms_per_step": r2["ms_per_step"], "roofline_frac": r2["glups"] * BYTES_PER_UPDATE / world / hbm_peak()[0],
+                       "e2e": e2["glups"], "gpu_launches": r2["launches"], "note": note}}
     if rank == 0:
         peak, how = hbm_peak()
         achieved = res["glups"] * BYTES_PER_UPDATE / world      # GB/s per GPU

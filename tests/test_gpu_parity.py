@@ -241,6 +241,27 @@ def test_row_slabs_over_nvlink_equal_single_gpu(lbm, ngpus, grid, steps):
     assert np.all(np.isfinite(pr))
 
 
+@pytest.mark.parametrize("ngpus,grid,steps", [(2, "4096x1024", 60), (4, "8192x1024", 40), (8, "16384x1024", 30), (2, "16384x1024", 30)])
+def test_baseline_slab_configs_equal_single_gpu(lbm, ngpus, grid, steps):
+    """BASELINE.json's row-decomposed configurations at their full sizes (4096x1024 on 2 GPUs, 8192x1024
+    on 4, 16384x1024 on 8): the N-slab lattice equals the single-GPU lattice bit for bit, and both keep the
+    total mass (the size-independent property the oracle cannot check at this size in seconds)."""
+    if _ngpu(lbm) < ngpus:
+        pytest.skip(f"needs {ngpus} GPUs")
+    p, mask, lines = load_grid(grid)
+    with make(lbm, p, mask, lines, iters=steps) as one:
+        m0 = float(one.total_density())
+        one.run(steps)
+        f1, av1, m1 = one.cells(), one.av_vels(), float(one.total_density())
+    with make(lbm, p, mask, lines, iters=steps, ngpus=ngpus) as many:
+        assert many.num_slabs() == ngpus
+        many.run(steps)
+        fn, avn, mn = many.cells(), many.av_vels(), float(many.total_density())
+    assert np.array_equal(f1, fn)
+    np.testing.assert_allclose(avn, av1, rtol=3e-7)
+    assert abs(m1 - m0) / m0 < 1e-6 and abs(mn - m0) / m0 < 1e-6
+
+
 @pytest.mark.parametrize("nx,ny,ngpus", [(256, 37, 2), (132, 5, 2), (256, 9, 4), (4, 3, 3), (256, 9, 8), (1024, 8, 8)])
 def test_slabs_random_state_matches_oracle(lbm, oracle, nx, ny, ngpus):
     """Random states on thin slabs (down to ONE row per GPU, where a task pulls both halo sides and the
