@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <chrono>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
@@ -527,8 +528,18 @@ int lbm_create(lbm_ctx** out, const lbm_params* params, const int* obstacles, in
     c->size = c->nslabs = ngpus;
     c->rank0 = 0;
     c->slabs.resize(ngpus);
+    const bool report = env_int("LBM_REPORT", 0) != 0;      // set-up phase times on stderr (host clock)
+    auto now = [] { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+    const double t0 = now();
+    cudaSetDevice(first);
+    cudaFree(nullptr);                                      // creates the primary context
+    const double t1 = now();
     int rc = configure_engine(c, first);
+    const double t2 = now();
     for (int r = 0; r < ngpus && !rc; ++r) rc = slab_create(c, c->slabs[r], r, first + r, obstacles);
+    if (report)
+        fprintf(stderr, "lbm_create: context %.3f s, engine set-up %.3f s, %d slab(s) (plan, allocation, uploads enqueued) %.3f s\n",
+                t1 - t0, t2 - t1, ngpus, now() - t2);
     // ring links over NVLink peer access (the reference's rank_up / rank_down, d2q9-bgk.c:501-502)
     for (int r = 0; r < ngpus && !rc && ngpus > 1; ++r) {
         Slab& s = c->slabs[r];

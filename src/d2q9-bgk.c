@@ -179,6 +179,9 @@ int main(int argc, char* argv[])
     read_params(paramfile, &p);
     int lines = 0;
     int* mask = read_obstacles(obstaclefile, &p, &lines);
+    const double parse_toc = wall();
+    const int visible = lbm_device_count();   /* first CUDA call: driver initialisation happens here */
+    const double driver_toc = wall();
 
     int ngpus = 1;
     const char* env = getenv("LBM_NGPUS");
@@ -257,6 +260,8 @@ int main(int argc, char* argv[])
         const double updates = (double)n * p.max_iters;
         const int slabs = lbm_num_slabs(ctx);
         fprintf(stderr, "engine: %s\n", lbm_describe(ctx));
+        fprintf(stderr, "init: parse %.3f s, CUDA driver start-up %.3f s (%d device(s) visible), lbm_create %.3f s\n",
+                parse_toc - init_tic, driver_toc - parse_toc, visible, init_toc - driver_toc);
         fprintf(stderr, "GLUPS (wall-clock compute window): %.3f\n", updates / (comp_toc - comp_tic) / 1e9);
         fprintf(stderr, "GLUPS (CUDA events):               %.3f on %d GPU(s)\n", updates / (ms * 1e-3) / 1e9, slabs);
         fprintf(stderr, "algorithmic HBM traffic: %.1f GB/s per GPU (72 B per cell update)\n",
