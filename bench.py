@@ -255,24 +255,35 @@ def time_e2e(lbm, torch, grid, iters, steps, rank, world, dist):
     if world > 1:
         dist.barrier()
     t0 = time.perf_counter()
+    ph = {"create": 0.0, "connect": 0.0, "run": 0.0, "download": 0.0, "reduce": 0.0, "destroy": 0.0}   # host seconds, this rank
     for _ in range(steps):
+        ta = time.perf_counter()
         if world > 1:
             lat = lbm.Lattice(p["nx"], p["ny"], iters, p["density"], p["accel"], p["omega"], mask, obstacle_lines=lines,
                               rank=rank, size=world, device=torch.cuda.current_device())
+            tb = time.perf_counter()
             up, down, _ = ring.exchange_blobs(dist, torch, lat.rank_export(), rank, world, device="cuda")
             lat.rank_connect(up, down)
         else:
             lat = lbm.Lattice(p["nx"], p["ny"], iters, p["density"], p["accel"], p["omega"], mask, obstacle_lines=lines)
+            tb = time.perf_counter()
+        tc = time.perf_counter()
         lat.run(iters)
-        av = lat.av_vels()
+        av = lat.av_vels()                   # waits for the run
+        td = time.perf_counter()
         f = lat.cells()
+        te = time.perf_counter()
         if world > 1:
             av = ring.reduce_av_vels(dist, torch, av, lat.inv_free_cells(), device="cuda")   # reference :445-446
             dist.barrier()                   # neighbours must be done with my halo rows before I free them
+        tf = time.perf_counter()
         a, b = lat.transfer_bytes()
         h2d += a
         d2h += b
         lat.close()
+        tg = time.perf_counter()
+        for k, v in zip(ph, (tb - ta, tc - tb, td - tc, te - td, tf - te, tg - tf)):
+            ph[k] += v / steps
         assert np.isfinite(av).all() and np.isfinite(f[:, ::64, ::64]).all()
     torch.cuda.synchronize()
     if world > 1:
@@ -285,7 +296,8 @@ def time_e2e(lbm, torch, grid, iters, steps, rank, world, dist):
         dist.all_reduce(t)
         wall, h2d, d2h = float(tm[0]), float(t[1]), float(t[2])
     updates = float(p["nx"]) * p["ny"] * iters * steps
-    return dict(glups=updates / wall / 1e9, h2d=int(h2d / steps), d2h=int(d2h / steps))
+    return dict(glups=updates / wall / 1e9, h2d=int(h2d / steps), d2h=int(d2h / steps),
+                phases={k: round(v, 4) for k, v in ph.items()})
 
 
 def main():
@@ -337,7 +349,7 @@ def main():
                "BASELINE.json's weak-scaling configuration for this GPU count (2.1 M cells per GPU)"
         also = {head: {"value": r2["glups"], "unit": "GLUPS", "iters_per_step": hi, "steps": max(3, args.steps),
                        "ms_per_step": r2["ms_per_step"], "roofline_frac": r2["glups"] * BYTES_PER_UPDATE / world / hbm_peak()[0],
-                       "e2e": e2["glups"], "gpu_launches": r2["launches"], "note": note}}
+                       "e2e": e2["glups"], "e2e_phases_s": e2["phases"], "gpu_launches": r2["launches"], "note": note}}
     if rank == 0:
         peak, how = hbm_peak()
         achieved = res["glups"] * BYTES_PER_UPDATE / world      # GB/s per GPU
@@ -356,6 +368,7 @@ def main():
                              "note": "achieved = 72 B x cell updates of one persistent launch / its CUDA-event time, per GPU; "
                                      "traffic = ncu dram bytes per cell update (profiles/traffic.json) x updates per launch per GPU"},
                 "e2e": {"value": e2e["glups"], "unit": "GLUPS", "h2d_bytes_per_step": e2e["h2d"], "d2h_bytes_per_step": e2e["d2h"],
+                        "phases_s": e2e["phases"],
                         "note": "lbm_create + lbm_run + lbm_get_av_vels + lbm_get_cells + lbm_destroy per step, host buffers"},
                 "gpu_launches": res["launches"], "clocks": res["clocks"], "wall_s_timed_region": res["wall_s"]}
         if also:

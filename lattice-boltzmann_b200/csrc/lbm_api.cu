@@ -4,13 +4,16 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <atomic>
 #include <chrono>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <stdexcept>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../../include/lbm_b200.h"
@@ -90,7 +93,6 @@ struct lbm_ctx {
     float last_ms = 0.f;
     int last_launches = 0;
     long long h2d_bytes = 0, d2h_bytes = 0;   // host<->device traffic issued through this context
-    std::vector<int> obstacles;   // host copy (ny*nx) kept for final-state / diagnostics
     char desc[512] = "";
 };
 
@@ -250,31 +252,153 @@ int env_int(const char* name, int dflt)
     return (v && *v) ? atoi(v) : dflt;
 }
 
+// Runs fn(begin, end) over [0, n) on a few host threads when the range is large (set-up work on the
+// 16384x1024 lattice: 16 M obstacle ints to count and pack; downloads of hundreds of MB).
+template <class F>
+void host_parallel(size_t n, size_t grain, F fn)
+{
+    unsigned hw = std::thread::hardware_concurrency();
+    size_t nt = std::min<size_t>(std::min<size_t>(hw ? hw : 1, 8), n / std::max<size_t>(grain, 1));
+    if (const char* e = getenv("LBM_HOST_THREADS")) nt = std::min<size_t>(nt, (size_t)std::max(1, atoi(e)));
+    if (nt <= 1) { fn((size_t)0, n); return; }
+    std::vector<std::thread> th;
+    for (size_t t = 1; t < nt; ++t) th.emplace_back([=] { fn(n * t / nt, n * (t + 1) / nt); });
+    fn((size_t)0, n / nt);
+    for (auto& x : th) x.join();
+}
+
 // Packs rows [row_start-1, row_start+rows] (periodic) of the 0/1 obstacle array to bits.
 std::vector<unsigned char> pack_mask(const int* obst, int nx, int ny, int row_start, int rows, int pitch)
 {
     std::vector<unsigned char> m((size_t)(rows + 2) * pitch, 0);
-    for (int h = 0; h < rows + 2; ++h) {
-        const int gy = ((row_start - 1 + h) % ny + ny) % ny;
-        for (int x = 0; x < nx; ++x)
-            if (obst[(size_t)gy * nx + x]) m[(size_t)h * pitch + (x >> 3)] |= (unsigned char)(1u << (x & 7));
-    }
+    host_parallel((size_t)(rows + 2), (size_t)std::max(1, (1 << 20) / nx), [&](size_t h0, size_t h1) {
+        for (size_t h = h0; h < h1; ++h) {
+            const int gy = ((row_start - 1 + (int)h) % ny + ny) % ny;
+            const int* row = obst + (size_t)gy * nx;
+            unsigned char* out = m.data() + h * pitch;
+            int x = 0;
+            for (; x + 8 <= nx; x += 8) {
+                unsigned b = 0;
+                for (int i = 0; i < 8; ++i) b |= (unsigned)(row[x + i] != 0) << i;
+                out[x >> 3] = (unsigned char)b;
+            }
+            for (; x < nx; ++x)
+                if (row[x]) out[x >> 3] |= (unsigned char)(1u << (x & 7));
+        }
+    });
     return m;
+}
+
+// ---- large device -> host downloads (collate, d2q9-bgk.c:395-447) -------------------------------
+// A plain cudaMemcpy of hundreds of MB into fresh pageable memory runs at ~4 GB/s on the B200 boxes
+// (first-touch page faults and a single staging thread; bench.py e2e phase "download").  Large
+// downloads instead go through pinned staging chunks: a few host threads each take every nt-th chunk,
+// D2H it asynchronously on their own stream into one of two pinned buffers and copy the previous
+// chunk out to the caller's memory meanwhile.  The pinned buffers live in a process-wide pool.
+struct Piece { void* dst; const void* src; size_t bytes; };
+constexpr size_t kChunkBytes = (size_t)4 << 20;
+std::mutex g_pin_mutex;
+std::vector<void*> g_pin_pool;
+
+void* pin_acquire()
+{
+    {
+        std::lock_guard<std::mutex> g(g_pin_mutex);
+        if (!g_pin_pool.empty()) { void* p = g_pin_pool.back(); g_pin_pool.pop_back(); return p; }
+    }
+    void* p = nullptr;
+    if (cudaHostAlloc(&p, kChunkBytes, cudaHostAllocPortable) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    return p;
+}
+void pin_release(void* p)
+{
+    if (!p) return;
+    std::lock_guard<std::mutex> g(g_pin_mutex);
+    g_pin_pool.push_back(p);
+}
+
+int download(int device, cudaStream_t stream, const std::vector<Piece>& pieces)
+{
+    size_t total = 0;
+    std::vector<Piece> chunks;
+    for (const Piece& pc : pieces) {
+        total += pc.bytes;
+        for (size_t o = 0; o < pc.bytes; o += kChunkBytes)
+            chunks.push_back({(char*)pc.dst + o, (const char*)pc.src + o, std::min(kChunkBytes, pc.bytes - o)});
+    }
+    int nt = (int)std::min<size_t>(4, chunks.size() / 4);
+    if (const char* e = getenv("LBM_HOST_THREADS")) nt = std::min(nt, std::max(1, atoi(e)));
+    if (total < ((size_t)32 << 20) || nt < 1 || env_int("LBM_PLAIN_DOWNLOAD", 0)) {      // small: the plain path
+        for (const Piece& pc : pieces) CK(cudaMemcpyAsync(pc.dst, pc.src, pc.bytes, cudaMemcpyDeviceToHost, stream));
+        CK(cudaStreamSynchronize(stream));
+        return 0;
+    }
+    std::vector<cudaError_t> err(nt, cudaSuccess);
+    auto worker = [&](int t) {
+        cudaError_t e = cudaSetDevice(device);
+        cudaStream_t st = nullptr;
+        cudaEvent_t ev[2] = {nullptr, nullptr};
+        void* pin[2] = {pin_acquire(), pin_acquire()};
+        if (e == cudaSuccess && (!pin[0] || !pin[1])) e = cudaErrorMemoryAllocation;
+        if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking);
+        for (int i = 0; i < 2 && e == cudaSuccess; ++i) e = cudaEventCreateWithFlags(&ev[i], cudaEventDisableTiming);
+        long prev = -1;
+        int k = 0;
+        for (size_t i = (size_t)t; e == cudaSuccess && i < chunks.size(); i += (size_t)nt, ++k) {
+            e = cudaMemcpyAsync(pin[k & 1], chunks[i].src, chunks[i].bytes, cudaMemcpyDeviceToHost, st);
+            if (e == cudaSuccess) e = cudaEventRecord(ev[k & 1], st);
+            if (prev >= 0 && e == cudaSuccess) {
+                e = cudaEventSynchronize(ev[(k - 1) & 1]);
+                if (e == cudaSuccess) memcpy(chunks[prev].dst, pin[(k - 1) & 1], chunks[prev].bytes);
+            }
+            prev = (long)i;
+        }
+        if (prev >= 0 && e == cudaSuccess) {
+            e = cudaEventSynchronize(ev[(k - 1) & 1]);
+            if (e == cudaSuccess) memcpy(chunks[prev].dst, pin[(k - 1) & 1], chunks[prev].bytes);
+        }
+        if (st) cudaStreamSynchronize(st);
+        for (int i = 0; i < 2; ++i) if (ev[i]) cudaEventDestroy(ev[i]);
+        if (st) cudaStreamDestroy(st);
+        pin_release(pin[0]);
+        pin_release(pin[1]);
+        err[t] = e;
+    };
+    CK(cudaStreamSynchronize(stream));          // what is downloaded was produced on `stream`
+    std::vector<std::thread> th;
+    for (int t = 1; t < nt; ++t) th.emplace_back(worker, t);
+    worker(0);
+    for (auto& x : th) x.join();
+    for (int t = 0; t < nt; ++t)
+        if (err[t] != cudaSuccess) { cudaGetLastError(); return fail("download: %s", cudaGetErrorString(err[t])); }
+    return 0;
 }
 
 void slab_free(Slab& s)
 {
     if (s.stream == nullptr && s.buf[0] == nullptr) return;
+    const bool report = getenv("LBM_REPORT") && atoi(getenv("LBM_REPORT")) > 1;
+    auto now = [] { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+    const double t0 = now();
     cudaSetDevice(s.device);
     if (s.graph) cudaGraphExecDestroy(s.graph);
     if (s.ipc_ll_up) cudaIpcCloseMemHandle(s.ipc_ll_up);
     if (s.ipc_ll_down && s.ipc_ll_down != s.ipc_ll_up) cudaIpcCloseMemHandle(s.ipc_ll_down);
-    cudaFree(s.buf[0]); cudaFree(s.buf[1]); cudaFree(s.mask); cudaFree(s.sched); cudaFree(s.flags);
+    const double t1 = now();
+    cudaFree(s.buf[0]);
+    const double t2 = now();
+    cudaFree(s.buf[1]);
+    const double t3 = now();
+    cudaFree(s.mask); cudaFree(s.sched); cudaFree(s.flags);
     cudaFree(s.partials); cudaFree(s.tot); cudaFree(s.status); cudaFree(s.step_ptr); cudaFree(s.fields);
     cudaFree(s.scal); cudaFree(s.prof); cudaFree(s.ll_in);
+    const double t4 = now();
     if (s.ev_start) cudaEventDestroy(s.ev_start);
     if (s.ev_stop) cudaEventDestroy(s.ev_stop);
     if (s.stream) cudaStreamDestroy(s.stream);
+    if (report)
+        fprintf(stderr, "slab_free: graph/ipc %.4f, buf0 %.4f, buf1 %.4f, small buffers %.4f, events/stream %.4f s\n", t1 - t0,
+                t2 - t1, t3 - t2, t4 - t3, now() - t4);
     s = Slab();
 }
 
@@ -400,9 +524,13 @@ int count_cells(lbm_ctx* c, const int* obst)
 {
     const lbm_params& P = c->prm;
     const size_t n = (size_t)P.nx * P.ny;
-    c->obstacles.assign(obst, obst + n);
-    int blocked = 0;
-    for (size_t i = 0; i < n; ++i) blocked += (obst[i] != 0);
+    std::atomic<long long> total{0};
+    host_parallel(n, (size_t)1 << 20, [&](size_t i0, size_t i1) {
+        long long k = 0;
+        for (size_t i = i0; i < i1; ++i) k += (obst[i] != 0);
+        total += k;
+    });
+    const int blocked = (int)total.load();
     c->blocked_cells = blocked;
     // the reference divides by nx*ny - <obstacle file LINES> (d2q9-bgk.c:642)
     c->free_cells = P.nx * P.ny - (P.obstacle_lines >= 0 ? P.obstacle_lines : blocked);
@@ -797,11 +925,11 @@ int lbm_get_cells(lbm_ctx* c, float* const speeds[LBM_NSPEEDS])
     for (Slab& s : c->slabs) {
         CK(cudaSetDevice(s.device));
         const size_t row0 = c->rank_mode ? 0 : (size_t)s.plan.row_start;
+        std::vector<Piece> pieces;
         for (int k = 0; k < LBM_NSPEEDS; ++k)
-            CK(cudaMemcpyAsync(speeds[k] + row0 * nx, s.buf[c->par] + k * s.dev.ps + nx,
-                               sizeof(float) * (size_t)s.plan.rows * nx, cudaMemcpyDeviceToHost, s.stream));
+            pieces.push_back({speeds[k] + row0 * nx, s.buf[c->par] + k * s.dev.ps + nx, sizeof(float) * (size_t)s.plan.rows * nx});
+        if (download(s.device, s.stream, pieces)) return 1;
         c->d2h_bytes += (long long)LBM_NSPEEDS * sizeof(float) * s.plan.rows * nx;
-        CK(cudaStreamSynchronize(s.stream));
     }
     return 0;
 }
@@ -844,12 +972,13 @@ int lbm_get_final_state(lbm_ctx* c, float* ux, float* uy, float* u, float* press
         k_final_state<<<(unsigned)((n + 255) / 256), 256, 0, s.stream>>>(s.dev, c->par, c->prm.density, dv[0], dv[1], dv[2], dv[3]);
         CK(cudaGetLastError());
         const size_t row0 = c->rank_mode ? 0 : (size_t)s.plan.row_start;
+        std::vector<Piece> pieces;
         for (int i = 0; i < 4; ++i)
             if (host[i]) {
-                CK(cudaMemcpyAsync(host[i] + row0 * nx, dv[i], sizeof(float) * n, cudaMemcpyDeviceToHost, s.stream));
+                pieces.push_back({host[i] + row0 * nx, dv[i], sizeof(float) * n});
                 c->d2h_bytes += (long long)sizeof(float) * n;
             }
-        CK(cudaStreamSynchronize(s.stream));
+        if (download(s.device, s.stream, pieces)) return 1;
     }
     return 0;
 }

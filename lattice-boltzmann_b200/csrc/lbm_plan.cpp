@@ -102,10 +102,15 @@ Layout make_layout(int tpr, int rows, int ctas, bool edge_rows, int edge_weight_
     const int64_t T = best.tasks();
     const int we = (edge_rows && rows > 2) ? edge_weight_16 : 16;
     std::vector<int64_t> cum(T + 1, 0);
-    for (int64_t q = 0; q < T; ++q) {
-        int lr, ch;
-        best.task_at(q, &lr, &ch);
-        cum[q + 1] = cum[q] + ((edge_rows && (lr == 0 || lr == rows - 1)) ? we : 16);
+    {
+        int64_t q = 0;                            // strip by strip, row-major inside a strip
+        for (int s = 0; s < best.strips; ++s) {
+            const int w = best.c0[s + 1] - best.c0[s];
+            for (int lr = 0; lr < rows; ++lr) {
+                const int wt = (edge_rows && (lr == 0 || lr == rows - 1)) ? we : 16;
+                for (int i = 0; i < w; ++i, ++q) cum[q + 1] = cum[q] + wt;
+            }
+        }
     }
     best.cut.assign(ctas + 1, 0);
     for (int b = 1; b < ctas; ++b) {
@@ -148,29 +153,45 @@ SlabPlan make_plan(int nx, int ny, int rank, int size, int ctas)
     p.dep_begin.assign(G + 1, 0);
     p.task_order.reserve(T);
 
+    // owner of every task (flat id) and the tasks in sequence order, in one pass over the strips
+    std::vector<int> own(T), seq(T);
+    {
+        int64_t q = 0;
+        int b = 0;
+        for (int s = 0; s < L.strips; ++s)
+            for (int lr = 0; lr < p.rows; ++lr)
+                for (int ch = L.c0[s]; ch < L.c0[s + 1]; ++ch, ++q) {
+                    while (q >= L.cut[b + 1]) ++b;
+                    own[lr * p.tpr + ch] = b;
+                    seq[q] = lr * p.tpr + ch;
+                }
+    }
+
+    std::vector<int> interior, boundary, edge, dep, stamp(G, -1);
     for (int b = 0; b < G; ++b) {
-        const int64_t lo = L.cut[b], hi = L.cut[b + 1];
-        std::vector<int> interior, boundary, edge;
-        std::set<int> dep;
-        for (int64_t q = lo; q < hi; ++q) {
-            int lr, ch;
-            L.task_at(q, &lr, &ch);
+        interior.clear(); boundary.clear(); edge.clear(); dep.clear();
+        for (int64_t q = L.cut[b]; q < L.cut[b + 1]; ++q) {
+            const int t = seq[q], lr = t / p.tpr, ch = t % p.tpr;
             bool inside = true;
             for (int dy = -1; dy <= 1; ++dy) {
+                int r2 = lr + dy;
+                if (r2 < 0 || r2 >= p.rows) {
+                    if (!single) { inside = false; continue; }   // remote row: tagged halo slots, no flag
+                    r2 = (r2 + p.rows) % p.rows;
+                }
                 for (int dx = -1; dx <= 1; ++dx) {
                     const int c2 = (ch + dx + p.tpr) % p.tpr;
-                    int r2 = lr + dy;
-                    if (r2 < 0 || r2 >= p.rows) {
-                        if (!single) { inside = false; continue; }   // remote row: tagged halo slots, no flag
-                        r2 = (r2 + p.rows) % p.rows;
+                    const int o = own[r2 * p.tpr + c2];
+                    if (o != b) {
+                        inside = false;
+                        if (stamp[o] != b) { stamp[o] = b; dep.push_back(o); }
                     }
-                    const int o = L.owner(r2, c2);
-                    if (o != b) { inside = false; dep.insert(o); }
                 }
             }
             const bool is_edge = !single && (lr == 0 || lr == p.rows - 1);
-            (inside ? interior : is_edge ? edge : boundary).push_back(lr * p.tpr + ch);
+            (inside ? interior : is_edge ? edge : boundary).push_back(t);
         }
+        std::sort(dep.begin(), dep.end());
         p.n_interior[b] = (int)interior.size();
         p.n_edge[b] = (int)edge.size();
         p.task_order.insert(p.task_order.end(), interior.begin(), interior.end());

@@ -121,6 +121,28 @@ def test_mass_conservation_and_obstacle_invariants_full_size(lbm, grid, steps):
     assert np.all(np.isfinite(pr))
 
 
+def test_pipelined_download_equals_plain_copy(lbm, monkeypatch):
+    """Downloads above 32 MB stream through pinned staging chunks on several host threads (collate,
+    d2q9-bgk.c:395-447); the result must be byte-identical to a plain cudaMemcpy, for the 9 planes and
+    for the 4 final-state fields, on a lattice whose planes are not a multiple of the 4 MB chunk."""
+    p, mask, lines = load_grid("4096x1024")
+    nx, ny = 4096 + 4, 1000 + 3
+    rng = np.random.default_rng(5)
+    m = (rng.random((ny, nx)) < 0.01).astype(np.int32)
+    with lbm.Lattice(nx, ny, 12, p["density"], p["accel"], p["omega"], m) as lat:
+        lat.run(12)
+        monkeypatch.setenv("LBM_PLAIN_DOWNLOAD", "1")
+        f0, s0 = lat.cells(), lat.final_state()
+        monkeypatch.setenv("LBM_PLAIN_DOWNLOAD", "0")
+        f1, s1 = lat.cells(), lat.final_state()
+        monkeypatch.setenv("LBM_HOST_THREADS", "1")
+        f2 = lat.cells()
+    assert f0.nbytes > (32 << 20) and np.array_equal(f0, f1) and np.array_equal(f0, f2)
+    for a, b in zip(s0, s1):
+        assert np.array_equal(a, b)
+    assert np.isfinite(f0).all() and len(np.unique(f0[:, ::7, ::13])) > 1000
+
+
 def test_errors_are_reported(lbm):
     p, mask, lines = load_grid("128x128")
     with make(lbm, p, mask, lines, iters=10) as lat:
