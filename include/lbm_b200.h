@@ -55,8 +55,10 @@ typedef struct lbm_options {
                            2 = fast: FMA contraction allowed (within check.py's tolerance) */
     int ctas_per_sm;    /* 0 = auto */
     int threads_per_cta;/* 0 = auto (multiple of 32) */
-    int engine;         /* 0 = auto; 1 = persistent neighbour-synchronised kernel;
-                           2 = one launch per timestep (CUDA-graph replayed) */
+    int engine;         /* 0 = auto (3 where it applies, else 1); 1 = persistent neighbour-synchronised
+                           kernel; 2 = one launch per timestep (CUDA-graph replayed); 3 = dataflow over
+                           tagged records: one resident warp per 128-cell task, single lattices of at
+                           most ~2300 tasks (128x128 ... 512x512) */
     int first_device;   /* first CUDA device ordinal used (single-process multi-GPU uses
                            first_device .. first_device+ngpus-1) */
 } lbm_options;

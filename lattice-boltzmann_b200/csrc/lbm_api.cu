@@ -62,6 +62,7 @@ struct Slab {
     cudaGraphExec_t graph = nullptr;
     int graph_steps = 0;
     int graph_par = -1;
+    uint4* rec = nullptr;          // engine 3: the lattice as tagged records [parity 2][row][group 3][plane 4][nx/4]
     uint4* ll_in = nullptr;        // inbound halo slots [parity 2][side 2][record 4][nx/4] (multi-slab only)
     // IPC (one-process-per-GPU mode): the ring neighbours' inbound halo slots
     void* ipc_ll_up = nullptr;
@@ -240,6 +241,11 @@ const void* persistent_pick(bool strict, bool ring)
     return strict ? (const void*)lbm::lbm_persistent_kernel<true, false, PROF> : (const void*)lbm::lbm_persistent_kernel<false, false, PROF>;
 }
 
+const void* dataflow_fn(bool strict)
+{
+    return strict ? (const void*)lbm::lbm_dataflow_kernel<true> : (const void*)lbm::lbm_dataflow_kernel<false>;
+}
+
 // LBM_PROFILE=1 selects the instantiations that carry the per-warp cycle counters
 const void* persistent_fn(bool strict, bool ring)
 {
@@ -391,7 +397,7 @@ void slab_free(Slab& s)
     const double t3 = now();
     cudaFree(s.mask); cudaFree(s.sched); cudaFree(s.flags);
     cudaFree(s.partials); cudaFree(s.tot); cudaFree(s.status); cudaFree(s.step_ptr); cudaFree(s.fields);
-    cudaFree(s.scal); cudaFree(s.prof); cudaFree(s.ll_in);
+    cudaFree(s.scal); cudaFree(s.prof); cudaFree(s.ll_in); cudaFree(s.rec);
     const double t4 = now();
     if (s.ev_start) cudaEventDestroy(s.ev_start);
     if (s.ev_stop) cudaEventDestroy(s.ev_stop);
@@ -413,9 +419,21 @@ int configure_engine(lbm_ctx* c, int device)
     const int sms = prop.multiProcessorCount;
     c->strict = (c->opt.strict_fp != 2);
     if (env_int("LBM_FAST_FP", 0)) c->strict = false;
-    c->engine = c->opt.engine ? c->opt.engine : env_int("LBM_ENGINE", 1);
-    if (c->engine != 1 && c->engine != 2) return fail("unknown engine %d", c->engine);
+    c->engine = c->opt.engine ? c->opt.engine : env_int("LBM_ENGINE", 0);
+    if (c->engine < 0 || c->engine > 3) return fail("unknown engine %d", c->engine);
     if (c->engine == 2 && c->size > 1) return fail("engine 2 (launch per timestep) supports a single slab only");
+    if (c->engine == 3 && c->size > 1) return fail("engine 3 (dataflow over tagged records) supports a single slab only");
+    // engine 3 needs every warp-task on its own resident warp (one warp per block) and keeps one partial
+    // sum per task and step; auto picks it whenever the lattice is small enough for both
+    const long long tasks = (long long)((c->prm.nx + lbm::kTaskCells - 1) / lbm::kTaskCells) * c->prm.ny;
+    int occ3 = 0;
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ3, dataflow_fn(c->strict), 32, 0));
+    const bool fits3 = c->size == 1 && tasks <= (long long)occ3 * sms &&
+                       tasks * std::max(c->prm.max_iters, 1) * (long long)sizeof(double) <= (1LL << 30);
+    if (c->engine == 3 && !fits3)
+        return fail("engine 3 needs a single lattice of at most %lld warp-tasks (this one has %lld) and at most 1 GiB of per-step "
+                    "partial sums", (long long)occ3 * sms, tasks);
+    if (c->engine == 0) c->engine = fits3 ? 3 : 1;
     c->threads = c->opt.threads_per_cta ? c->opt.threads_per_cta : env_int("LBM_THREADS", 256);
     if (c->threads % 32 || c->threads < 32 || c->threads > 512) return fail("threads_per_cta must be a multiple of 32 in [32,512]");
     int per_sm = c->opt.ctas_per_sm ? c->opt.ctas_per_sm : env_int("LBM_CTAS_PER_SM", 2);
@@ -427,6 +445,11 @@ int configure_engine(lbm_ctx* c, int device)
     if (occ < 1) return fail("persistent kernel does not fit on an SM with %d threads", c->threads);
     per_sm = std::max(1, std::min(per_sm, occ));
     c->ctas_budget = sms * per_sm;
+    if (c->engine == 3) {                // one block of one warp per task
+        c->threads = 32;
+        c->ctas_budget = (int)tasks;
+        return 0;
+    }
     const int cap = env_int("LBM_MAX_CTAS", 0);
     if (cap > 0) c->ctas_budget = std::min(c->ctas_budget, cap);
     return 0;
@@ -467,6 +490,11 @@ int slab_create(lbm_ctx* c, Slab& s, int rank, int device, const int* obst)
         CK(cudaMalloc(&s.ll_in, sizeof(uint4) * 4 * (size_t)P.nx));
         CK(cudaMemsetAsync(s.ll_in, 0, sizeof(uint4) * 4 * (size_t)P.nx, s.stream));
     }
+    if (c->engine == 3) {  // tag 0 = never written
+        const size_t bytes = sizeof(uint4) * 2 * 3 * (size_t)pl.rows * P.nx;
+        CK(cudaMalloc(&s.rec, bytes));
+        CK(cudaMemsetAsync(s.rec, 0, bytes, s.stream));
+    }
     CK(cudaMemsetAsync(s.tot, 0, sizeof(double) * std::max(P.max_iters, 1), s.stream));
     CK(cudaMemsetAsync(s.status, 0, sizeof(int), s.stream));
     CK(cudaMemsetAsync(s.step_ptr, 0, sizeof(int), s.stream));
@@ -505,6 +533,7 @@ int slab_create(lbm_ctx* c, Slab& s, int rank, int device, const int* obst)
     d.aw1 = P.density * P.accel / 9.f;       // d2q9-bgk.c:237
     d.aw2 = P.density * P.accel / 36.f;      // d2q9-bgk.c:238
     d.ll_in = s.ll_in; d.ll_up = d.ll_down = nullptr;
+    d.rec = s.rec;
     d.task_begin = s.sched + o_tb; d.n_interior = s.sched + o_ni; d.n_edge = s.sched + o_ne; d.task_order = (const int2*)(s.sched + o_to);
     d.dep_begin = s.sched + o_db; d.deps = s.sched + o_dp;
     d.flags = s.flags;
@@ -553,7 +582,8 @@ void describe(lbm_ctx* c)
     const Slab& s = c->slabs[0];
     snprintf(c->desc, sizeof(c->desc),
              "engine=%s fp=%s slabs=%d/%d ctas/slab=%d threads/cta=%d tasks/slab=%d tasks/row=%d strips=%d interior=%.0f%%",
-             c->engine == 1 ? "persistent-neighbour-sync" : "launch-per-step-graph", c->strict ? "strict" : "fast",
+             c->engine == 1 ? "persistent-neighbour-sync" : c->engine == 3 ? "dataflow-tagged-records" : "launch-per-step-graph",
+             c->strict ? "strict" : "fast",
              c->nslabs, c->size, s.plan.num_ctas, c->threads, s.plan.num_tasks, s.plan.tpr, s.plan.strips,
              100.0 * lbm::interior_fraction(s.plan));
 }
@@ -791,6 +821,23 @@ static int run_engine2(lbm_ctx* c, int iters)
     return 0;
 }
 
+static int run_engine3(lbm_ctx* c, int iters)
+{
+    Slab& s = c->slabs[0];
+    CK(cudaSetDevice(s.device));
+    CK(cudaEventRecord(s.ev_start, s.stream));
+    int par0 = c->par, step0 = c->steps_done, it = iters;
+    unsigned base = c->base;
+    void* args[] = {(void*)&s.dev, (void*)&par0, (void*)&step0, (void*)&it, (void*)&base};
+    // cooperative only for the co-residency guarantee: every warp polls its neighbours' records
+    CK(cudaLaunchCooperativeKernel(dataflow_fn(c->strict), dim3(s.plan.num_tasks), dim3(32), args, 0, s.stream));
+    CK(cudaEventRecord(s.ev_stop, s.stream));
+    c->base += (unsigned)iters + 1u;
+    if (iters & 1) c->par ^= 1;
+    c->last_launches = 1;
+    return 0;
+}
+
 static int run_engine1(lbm_ctx* c, int iters)
 {
     const void* fn = persistent_fn(c->strict, c->size > 1);
@@ -819,7 +866,7 @@ int lbm_run(lbm_ctx* c, int iters)
     if (c->steps_done + iters > c->prm.max_iters)
         return fail("lbm_run: %d + %d steps exceed max_iters=%d", c->steps_done, iters, c->prm.max_iters);
     if (c->size > 1 && !c->connected) return fail("lbm_run: ring neighbours not connected (call lbm_rank_connect)");
-    const int rc = (c->engine == 1) ? run_engine1(c, iters) : run_engine2(c, iters);
+    const int rc = (c->engine == 1) ? run_engine1(c, iters) : (c->engine == 3) ? run_engine3(c, iters) : run_engine2(c, iters);
     if (rc) return rc;
     c->steps_done += iters;
     return 0;
@@ -862,7 +909,7 @@ namespace {
 // Folds the persistent engine's per-CTA partials of steps [finalized, steps_done) into tot[].
 int fold_partials(lbm_ctx* c, Slab& s)
 {
-    if (c->engine != 1 || s.finalized_steps >= c->steps_done) return 0;
+    if (c->engine == 2 || s.finalized_steps >= c->steps_done) return 0;
     CK(cudaSetDevice(s.device));
     const int n = c->steps_done - s.finalized_steps;
     k_fold_partials<<<(n + 7) / 8, 256, 0, s.stream>>>(s.partials, s.tot, s.plan.num_ctas, s.finalized_steps, c->steps_done);

@@ -450,4 +450,150 @@ __global__ void __launch_bounds__(512, 1) lbm_persistent_kernel(SlabDev d, int p
     }
 }
 
+// ------------------------------------------------------------------------------------------
+// Engine 3: dataflow over tagged records - the small-lattice engine.
+// On a lattice with no more warp-tasks than the GPU holds resident warps (128x128 ... 512x512) a
+// timestep of engine 1 is ONE dependency chain: store, fence, release flag, poll flag, load, compute;
+// the arithmetic is a small part of it.  Here every warp owns one task for the whole run and the lattice
+// itself lives in the tagged 16-byte record format of the halo slots (lbm_device.cuh): a row's 9
+// populations are kept as three record groups by DESTINATION row - northbound (f2,f5,f6: read by the row
+// above), southbound (f4,f7,f8: read by the row below), horizontal (f0,f1,f3: read by the row itself) -
+// each group 4 record planes of nx/4 records {v,v,v,tag}.  A warp polls the three groups it pulls from
+// until all carry the step's tag, collides, and stores its own three groups with tag + 1 into the other
+// parity.  No flag, no fence, no barrier, no CTA: one warp per block.  A record is rewritten two steps
+// later; by then every reader has published the output of the step that read it, which the writer had
+// to see before it could compute (same argument as for the halo slots).
+// The SoA lattice stays the canonical state BETWEEN runs: the prologue converts the warp's own row
+// segment into records (after the in-place accelerate_flow of the first step), the last step stores
+// SoA.  Per step every warp leaves its own partial sum of |u| (partials[step][task], folded later in a
+// fixed order).  Single lattice only.
+// ------------------------------------------------------------------------------------------
+constexpr int kRecNorthbound = 0, kRecSouthbound = 1, kRecHorizontal = 2;
+
+__device__ __forceinline__ uint4* rec_group(const SlabDev& d, int par, int row, int kind)
+{
+    return d.rec + ((size_t)(par * d.rows + row) * 3 + kind) * (size_t)d.nx;
+}
+
+// One record group of this lane's 4 cells (+ the west / east element on the lanes that need one);
+// returns whether every tag matched.  SIDE as in ll_pull: 0 = the west element is b3 and the east
+// element c0 (northbound and horizontal groups), 1 = west c3, east b0 (southbound group).
+template <int SIDE>
+__device__ __forceinline__ bool rec_take(const SlabDev& d, const uint4* base, const TaskGeom& g, unsigned tag, float4 (&v)[3],
+                                         float& w, float& e)
+{
+    const int Q = d.nx >> 2;
+    const uint4 *pq, *pw, *pe;
+    ll_addresses<SIDE>(d, base, g, pq, pw, pe);
+    const uint4 r0 = ld_record(pq), r1 = ld_record(pq + Q), r2 = ld_record(pq + 2 * Q), r3 = ld_record(pq + 3 * Q);
+    bool ok = r0.w == tag && r1.w == tag && r2.w == tag && r3.w == tag;
+    v[0] = make_float4(__uint_as_float(r0.x), __uint_as_float(r0.y), __uint_as_float(r0.z), __uint_as_float(r1.x));
+    v[1] = make_float4(__uint_as_float(r1.y), __uint_as_float(r1.z), __uint_as_float(r2.x), __uint_as_float(r2.y));
+    v[2] = make_float4(__uint_as_float(r2.z), __uint_as_float(r3.x), __uint_as_float(r3.y), __uint_as_float(r3.z));
+    if (g.need_w) { const uint4 q = ld_record(pw); ok = ok && q.w == tag; w = __uint_as_float(SIDE ? q.z : q.y); }
+    if (g.need_e) { const uint4 q = ld_record(pe); ok = ok && q.w == tag; e = __uint_as_float(SIDE ? q.y : q.z); }
+    return ok;
+}
+
+template <bool S>
+__global__ void __launch_bounds__(32) lbm_dataflow_kernel(SlabDev d, int par0, int step0, int iters, unsigned base)
+{
+    const int lane = threadIdx.x;
+    const int task = blockIdx.x;
+    const int2 td = make_int2(task / d.tpr, task % d.tpr);
+    const TaskGeom g = task_geom<false>(d, td, lane);
+    const int Q = d.nx >> 2, q = g.x0 >> 2;
+    const int row_s = g.lr == 0 ? d.rows - 1 : g.lr - 1, row_n = g.lr == d.rows - 1 ? 0 : g.lr + 1;
+    const unsigned ps = (unsigned)d.ps;
+    const unsigned mbyte = __ldg(d.mask + ((unsigned)(g.lr + 1) * (unsigned)d.mask_pitch + ((unsigned)g.xc >> 3)));
+    const unsigned nib = (mbyte >> (g.xc & 4)) & 0xFu;
+    const unsigned full = 0xffffffffu;
+
+    // ---- prologue: own row segment of the SoA lattice -> records of parity 0, tag base + 1
+    {
+        const float* src = d.buf[par0];
+        float4 v[9];
+#pragma unroll
+        for (int k = 0; k < 9; ++k) v[k] = ld_cg4(src + ((unsigned)k * ps + g.rc));
+        if (g.lr == d.accel_lr) {                       // accelerate_flow of the first step (d2q9-bgk.c:235-266)
+            float p[4][9];
+#pragma unroll
+            for (int k = 0; k < 9; ++k) { p[0][k] = v[k].x; p[1][k] = v[k].y; p[2][k] = v[k].z; p[3][k] = v[k].w; }
+#pragma unroll
+            for (int j = 0; j < 4; ++j) accelerate_cell(p[j], (nib >> j) & 1u, d.aw1, d.aw2);
+#pragma unroll
+            for (int k = 0; k < 9; ++k) v[k] = make_float4(p[0][k], p[1][k], p[2][k], p[3][k]);
+        }
+        if (g.active) {
+            st_halo(rec_group(d, 0, g.lr, kRecNorthbound) + q, Q, v[2], v[5], v[6], base + 1u);
+            st_halo(rec_group(d, 0, g.lr, kRecSouthbound) + q, Q, v[4], v[7], v[8], base + 1u);
+            st_halo(rec_group(d, 0, g.lr, kRecHorizontal) + q, Q, v[0], v[1], v[3], base + 1u);
+        }
+    }
+
+    for (int s = 0; s < iters; ++s) {
+        const unsigned tag = base + 1u + (unsigned)s;
+        const int rp = s & 1;
+        float4 cv[3], sv[3], nv[3];      // (f0,f1,f3) of the row; (f2,f5,f6) of the south row; (f4,f7,f8) of the north row
+        float w1 = 0.f, w5 = 0.f, w8 = 0.f, e3 = 0.f, e6 = 0.f, e7 = 0.f;
+        long long t0 = 0;
+        for (int tries = 0;; ++tries) {
+            bool ok = rec_take<0>(d, rec_group(d, rp, g.lr, kRecHorizontal), g, tag, cv, w1, e3);
+            ok = rec_take<0>(d, rec_group(d, rp, row_s, kRecNorthbound), g, tag, sv, w5, e6) && ok;
+            ok = rec_take<1>(d, rec_group(d, rp, row_n, kRecSouthbound), g, tag, nv, w8, e7) && ok;
+            if (__all_sync(full, ok)) break;
+            // give up warp-uniformly (another warp failed, or a neighbour never arrives)
+            if (tries == 0) t0 = clock64();
+            const bool late = clock64() - t0 > kSpinLimitCycles;
+            if (late) atomicExch(d.status, 2);
+            if (__any_sync(full, late || *(volatile int*)d.status != 0)) return;
+        }
+        const float4 c0 = cv[0], c1 = cv[1], c3 = cv[2], s2 = sv[0], s5 = sv[1], s6 = sv[2], n4 = nv[0], n7 = nv[1], n8 = nv[2];
+
+        // ---- lane-crossing elements by shuffle, pulled populations (d2q9-bgk.c:315): as process_task
+        float t;
+        t = __shfl_up_sync(full, c1.w, 1);   if (!g.need_w) w1 = t;
+        t = __shfl_up_sync(full, s5.w, 1);   if (!g.need_w) w5 = t;
+        t = __shfl_up_sync(full, n8.w, 1);   if (!g.need_w) w8 = t;
+        t = __shfl_down_sync(full, c3.x, 1); if (!g.need_e) e3 = t;
+        t = __shfl_down_sync(full, s6.x, 1); if (!g.need_e) e6 = t;
+        t = __shfl_down_sync(full, n7.x, 1); if (!g.need_e) e7 = t;
+        float p[4][9];
+        p[0][0] = c0.x; p[1][0] = c0.y; p[2][0] = c0.z; p[3][0] = c0.w;
+        p[0][1] = w1;   p[1][1] = c1.x; p[2][1] = c1.y; p[3][1] = c1.z;
+        p[0][2] = s2.x; p[1][2] = s2.y; p[2][2] = s2.z; p[3][2] = s2.w;
+        p[0][3] = c3.y; p[1][3] = c3.z; p[2][3] = c3.w; p[3][3] = e3;
+        p[0][4] = n4.x; p[1][4] = n4.y; p[2][4] = n4.z; p[3][4] = n4.w;
+        p[0][5] = w5;   p[1][5] = s5.x; p[2][5] = s5.y; p[3][5] = s5.z;
+        p[0][6] = s6.y; p[1][6] = s6.z; p[2][6] = s6.w; p[3][6] = e6;
+        p[0][7] = n7.y; p[1][7] = n7.z; p[2][7] = n7.w; p[3][7] = e7;
+        p[0][8] = w8;   p[1][8] = n8.x; p[2][8] = n8.y; p[3][8] = n8.z;
+
+        float usum = collide4<S>(p, nib, d.omega);
+        const bool last = (s + 1 == iters);
+        if (!last && g.lr == d.accel_lr) {              // accelerate_flow for the next step
+#pragma unroll
+            for (int j = 0; j < 4; ++j) accelerate_cell(p[j], (nib >> j) & 1u, d.aw1, d.aw2);
+        }
+        if (g.active) {
+            float4 o[9];
+#pragma unroll
+            for (int k = 0; k < 9; ++k) o[k] = make_float4(p[0][k], p[1][k], p[2][k], p[3][k]);
+            if (!last) {
+                st_halo(rec_group(d, rp ^ 1, g.lr, kRecNorthbound) + q, Q, o[2], o[5], o[6], tag + 1u);
+                st_halo(rec_group(d, rp ^ 1, g.lr, kRecSouthbound) + q, Q, o[4], o[7], o[8], tag + 1u);
+                st_halo(rec_group(d, rp ^ 1, g.lr, kRecHorizontal) + q, Q, o[0], o[1], o[3], tag + 1u);
+            } else {                                    // the run's result goes back to the SoA lattice
+                float* dst = d.buf[par0 ^ (iters & 1)];
+#pragma unroll
+                for (int k = 0; k < 9; ++k) st_cg4(dst + ((unsigned)k * ps + g.rc), o[k]);
+            }
+        } else {
+            usum = 0.f;
+        }
+        const double acc = warp_sum((double)usum);
+        if (lane == 0) d.partials[(long long)(step0 + s) * d.num_ctas + task] = acc;
+    }
+}
+
 }  // namespace lbm

@@ -24,7 +24,7 @@ def make(lbm, p, mask, lines=-1, iters=None, **kw):
                        p["omega"], mask, obstacle_lines=lines, **kw)
 
 
-@pytest.mark.parametrize("engine", [1, 2])
+@pytest.mark.parametrize("engine", [1, 2, 3])
 @pytest.mark.parametrize("nx,ny,walls", [(128, 128, True), (128, 256, False), (256, 64, True), (132, 40, False),
                                          (512, 16, False), (4, 3, False), (1024, 9, True)])
 def test_random_state_matches_oracle_bit_exact(lbm, oracle, engine, nx, ny, walls):
@@ -83,7 +83,8 @@ def test_full_runs_against_shipped_known_answers_and_reference(lbm, golden, grid
 def test_engines_and_split_runs_agree(lbm):
     p, mask, lines = load_grid("128x256")
     outs = []
-    for engine, chunks in ((1, [300]), (2, [300]), (1, [1, 99, 64, 136]), (2, [150, 150])):
+    for engine, chunks in ((1, [300]), (2, [300]), (1, [1, 99, 64, 136]), (2, [150, 150]), (3, [300]), (3, [1, 99, 64, 136]),
+                           (0, [2, 298])):
         with make(lbm, p, mask, lines, iters=300, engine=engine) as lat:
             for c in chunks:
                 lat.run(c)
