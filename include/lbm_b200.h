@@ -165,6 +165,9 @@ int lbm_allocate_rows(int ny, int size, int rank, int* row_start, int* rows);
  * neighbour owner is a dependency, mirror-flag indices agree between ring neighbours.
  * Needs no GPU.  Returns 0 if consistent. */
 int lbm_plan_selftest(int nx, int ny, int size, int ctas);
+/* Host set-up code (threaded obstacle count and bit-pack) against plain loops on a hashed obstacle
+ * array, for every slab of a `size`-way decomposition.  No device needed. */
+int lbm_host_selftest(int nx, int ny, int size, long long seed);
 
 /* Device self check of the kernel's exact division / square-root fast paths: evaluates them on
  * 2*n hashed operand pairs (whole accepted range, and LBM-like magnitudes) and counts results that

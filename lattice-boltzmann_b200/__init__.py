@@ -69,6 +69,7 @@ SYMBOLS = {
     "lbm_get_profile": (ctypes.c_int, [_P, ctypes.c_int, _P, ctypes.c_int, _IP, _IP]),
     "lbm_allocate_rows": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, ctypes.c_int, _IP, _IP]),
     "lbm_plan_selftest": (ctypes.c_int, [ctypes.c_int] * 4),
+    "lbm_host_selftest": (ctypes.c_int, [ctypes.c_int] * 3 + [ctypes.c_longlong]),
     "lbm_selftest_math": (ctypes.c_int, [ctypes.c_longlong, ctypes.c_longlong, ctypes.POINTER(ctypes.c_longlong)]),
     "lbm_create_rank": (ctypes.c_int, [ctypes.POINTER(_P), ctypes.POINTER(Params), _P, ctypes.c_int, ctypes.c_int,
                                        ctypes.c_int, ctypes.POINTER(Options)]),

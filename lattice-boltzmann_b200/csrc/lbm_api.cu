@@ -197,7 +197,7 @@ __global__ void k_fold_partials(const double* partials, double* tot, int num_cta
 // Brute-force check of the exact fast paths in lbm_device.cuh against the IEEE intrinsics.
 // Operands are hashed bit patterns: mode 0 spans the whole accepted range (and a little beyond it,
 // where the range tests must reject), mode 1 concentrates on LBM-like magnitudes (rho ~ 0.1).
-__device__ __forceinline__ unsigned mix32(unsigned long long x)
+__host__ __device__ __forceinline__ unsigned mix32(unsigned long long x)
 {
     x ^= x >> 33; x *= 0xff51afd7ed558ccdULL; x ^= x >> 33; x *= 0xc4ceb9fe1a85ec53ULL; x ^= x >> 33;
     return (unsigned)x;
@@ -626,6 +626,38 @@ int lbm_plan_selftest(int nx, int ny, int size, int ctas)
         if (next_row != ny) return fail("slabs cover %d of %d rows", next_row, ny);
     } catch (const std::exception& e) {
         return fail("%s", e.what());
+    }
+    return 0;
+}
+
+// Host set-up code without a device: the threaded obstacle count and bit-pack (count_cells, pack_mask)
+// against plain loops, on a hashed 0/1 array, for every slab of a `size`-way row decomposition.
+int lbm_host_selftest(int nx, int ny, int size, long long seed)
+{
+    if (nx < 1 || ny < 1 || size < 1 || size > ny) return fail("bad arguments");
+    std::vector<int> obst((size_t)nx * ny);
+    long long want = 0;
+    for (size_t i = 0; i < obst.size(); ++i) {
+        obst[i] = (mix32((unsigned long long)seed * 0x9E3779B97F4A7C15ULL + i) % 7u) == 0u ? 1 : 0;
+        want += obst[i];
+    }
+    lbm_ctx c;
+    c.prm.nx = nx; c.prm.ny = ny; c.prm.obstacle_lines = -1;
+    if (count_cells(&c, obst.data())) return 1;
+    if (c.blocked_cells != want) return fail("count_cells: %d blocked cells, expected %lld", c.blocked_cells, want);
+    const int pitch = ((nx + 7) / 8 + 15) / 16 * 16;
+    for (int r = 0; r < size; ++r) {
+        const lbm::SlabShape sh = lbm::allocate_rows(ny, size, r);
+        const std::vector<unsigned char> m = pack_mask(obst.data(), nx, ny, sh.row_start, sh.rows, pitch);
+        if (m.size() != (size_t)(sh.rows + 2) * pitch) return fail("pack_mask: wrong size");
+        for (int h = 0; h < sh.rows + 2; ++h) {
+            const int gy = ((sh.row_start - 1 + h) % ny + ny) % ny;
+            for (int x = 0; x < pitch * 8; ++x) {
+                const int bit = (m[(size_t)h * pitch + (x >> 3)] >> (x & 7)) & 1;
+                const int ref = x < nx ? obst[(size_t)gy * nx + x] : 0;
+                if (bit != ref) return fail("pack_mask: slab %d row %d x %d: bit %d, expected %d", r, h, x, bit, ref);
+            }
+        }
     }
     return 0;
 }

@@ -72,6 +72,22 @@ def test_planner_selfcheck(lbm, nx, ny, size):
         assert lib.lbm_plan_selftest(nx, ny, size, ctas) == 0, lib.lbm_last_error().decode()
 
 
+@pytest.mark.parametrize("nx,ny,size", [(128, 128, 1), (132, 40, 3), (4, 3, 3), (1028, 9, 2), (2048, 1031, 8), (16384, 1024, 8)])
+def test_host_setup_selfcheck(lbm, nx, ny, size):
+    """The threaded obstacle count and bit-pack of lbm_create against plain loops (no device needed),
+    with 1, 3 and the default number of host threads."""
+    lib = lbm.load_library()
+    for threads in ("1", "3", None):
+        if threads is None:
+            os.environ.pop("LBM_HOST_THREADS", None)
+        else:
+            os.environ["LBM_HOST_THREADS"] = threads
+        try:
+            assert lib.lbm_host_selftest(nx, ny, size, 7 + nx) == 0, lib.lbm_last_error().decode()
+        finally:
+            os.environ.pop("LBM_HOST_THREADS", None)
+
+
 def run_exe(*args, cwd=None):
     return subprocess.run([EXE, *args], capture_output=True, text=True, cwd=cwd)
 

@@ -41,15 +41,15 @@ def to_ms(v, u):
     return f * {"ns": 1e-6, "us": 1e-3, "ms": 1.0, "s": 1e3, "nsecond": 1e-6, "usecond": 1e-3, "msecond": 1.0, "second": 1e3}[u]
 
 
-def full_summary(tag, grid, steps):
-    rep = os.path.join(OUT, f"prof_persistent_{grid}.ncu-rep")
+def full_summary(tag, grid, steps, kind="persistent", config="1:256:2:1"):
+    rep = os.path.join(OUT, f"prof_{kind}_{grid}.ncu-rep")
     m = raw_page(rep)
     nx, ny = (int(v) for v in grid.split("x"))
     cells = nx * ny
-    lines = [f"# {tag} — ncu --set full of lbm_persistent_kernel<strict> on {grid} ({steps} timesteps in one launch)", "",
-             f"Command: `python tools/explore.py --grid {grid} --steps {steps} --reps 1 --configs 1:256:2:1` (2nd launch captured, "
+    lines = [f"# {tag} — ncu --set full of lbm_{kind}_kernel<strict> on {grid} ({steps} timesteps in one launch)", "",
+             f"Command: `python tools/explore.py --grid {grid} --steps {steps} --reps 1 --configs {config}` (2nd launch captured, "
              f"`-s 1 -c 1`), ncu --set full --clock-control none --import-source on (tools/profile_r01.sh). "
-             f"Report: gpurun_out/prof_persistent_{grid}.ncu-rep (scratch).", "",
+             f"Report: gpurun_out/prof_{kind}_{grid}.ncu-rep (scratch).", "",
              f"kernel: `{m['Kernel Name'][0]}`  grid {m.get('Grid Size', ('?',))[0]} block {m.get('Block Size', ('?',))[0]}", "",
              "| metric | value | unit |", "|---|---|---|"]
     for k in WANT:
@@ -74,7 +74,7 @@ def full_summary(tag, grid, steps):
               f"* DRAM traffic per launch (dram__bytes_read+write) = {(rd + wr) / 1e9:.3f} GB = {(rd + wr) / alg:.3f} x algorithmic "
               f"({(rd + wr) / (steps * cells):.1f} B per cell update)",
               f"* warp instructions per 128-cell task = {inst / tasks:.0f}  ({inst / tasks / 128:.2f} per cell per lane-quad x4)"]
-    with open(os.path.join(PROF, f"{tag}_ncu_persistent_{grid}.md"), "w") as fh:
+    with open(os.path.join(PROF, f"{tag}_ncu_{kind}_{grid}.md"), "w") as fh:
         fh.write("\n".join(lines) + "\n")
     return (rd + wr) / (steps * cells)
 
@@ -114,6 +114,8 @@ def main():
     per = {}
     for grid, steps in (("16384x1024", 40), ("1024x1024", 300)):
         per[grid] = round(full_summary(tag, grid, steps), 2)
+    if os.path.exists(os.path.join(OUT, "prof_dataflow_256x256.ncu-rep")):      # engine 3, L2-resident: not in traffic.json
+        full_summary(tag, "256x256", 2000, kind="dataflow", config="3:32:0:1")
     with open(os.path.join(PROF, "traffic.json"), "w") as fh:
         json.dump({"source": "ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum of one lbm_persistent_kernel launch / "
                              f"(timesteps x cells) - see profiles/{tag}_ncu_persistent_<grid>.md",
