@@ -87,6 +87,7 @@ struct lbm_ctx {
     int engine = 1;
     bool strict = true;
     int threads = 512;
+    int df_k = 1;            // engine 3: consecutive tasks per warp
     int ctas_budget = 0;     // persistent CTAs per slab (before clamping to the task count)
     size_t stage_bytes = 0;  // dynamic shared memory per persistent CTA
     int free_cells = 0;      // denominator of av_vels
@@ -241,9 +242,10 @@ const void* persistent_pick(bool strict, bool ring)
     return strict ? (const void*)lbm::lbm_persistent_kernel<true, false, PROF> : (const void*)lbm::lbm_persistent_kernel<false, false, PROF>;
 }
 
-const void* dataflow_fn(bool strict)
+const void* dataflow_fn(bool strict, bool multi)
 {
-    return strict ? (const void*)lbm::lbm_dataflow_kernel<true> : (const void*)lbm::lbm_dataflow_kernel<false>;
+    if (multi) return strict ? (const void*)lbm::lbm_dataflow_kernel<true, true> : (const void*)lbm::lbm_dataflow_kernel<false, true>;
+    return strict ? (const void*)lbm::lbm_dataflow_kernel<true, false> : (const void*)lbm::lbm_dataflow_kernel<false, false>;
 }
 
 // LBM_PROFILE=1 selects the instantiations that carry the per-warp cycle counters
@@ -427,12 +429,22 @@ int configure_engine(lbm_ctx* c, int device)
     // sum per task and step; auto picks it whenever the lattice is small enough for both
     const long long tasks = (long long)((c->prm.nx + lbm::kTaskCells - 1) / lbm::kTaskCells) * c->prm.ny;
     int occ3 = 0;
-    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ3, dataflow_fn(c->strict), 32, 0));
-    const bool fits3 = c->size == 1 && tasks <= (long long)occ3 * sms &&
-                       tasks * std::max(c->prm.max_iters, 1) * (long long)sizeof(double) <= (1LL << 30);
-    if (c->engine == 3 && !fits3)
-        return fail("engine 3 needs a single lattice of at most %lld warp-tasks (this one has %lld) and at most 1 GiB of per-step "
-                    "partial sums", (long long)occ3 * sms, tasks);
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ3, dataflow_fn(c->strict, false), 32, 0));
+    const long long warps3 = (long long)occ3 * sms;
+    const bool mem3 = tasks * std::max(c->prm.max_iters, 1) * (long long)sizeof(double) <= (2LL << 30);
+    // a warp owns 1 task, or several consecutive ones when the lattice has more tasks than resident warps.
+    // Measured (profiles/r01_small_lattice.md): 2 per warp still beats engine 1 by 2.3x (1024x512), 4 per warp
+    // loses to it (1024x1024: 73 vs 98 GLUPS) - auto stops at 2; a forced engine 3 may go to 8.
+    const int k_min = (int)((tasks + warps3 - 1) / std::max(warps3, 1LL));
+    const bool fits3 = c->size == 1 && k_min <= 2 && mem3;
+    c->df_k = k_min;
+    if (c->engine == 3) {
+        const int k = std::max(k_min, env_int("LBM_DF_TASKS_PER_WARP", 1));
+        if (c->size != 1 || !mem3 || k > 8)
+            return fail("engine 3 needs a single lattice of at most %lld warp-tasks (this one has %lld) and at most 2 GiB of "
+                        "per-step partial sums", 8 * warps3, tasks);
+        c->df_k = k;
+    }
     if (c->engine == 0) c->engine = fits3 ? 3 : 1;
     c->threads = c->opt.threads_per_cta ? c->opt.threads_per_cta : env_int("LBM_THREADS", 256);
     if (c->threads % 32 || c->threads < 32 || c->threads > 512) return fail("threads_per_cta must be a multiple of 32 in [32,512]");
@@ -534,6 +546,7 @@ int slab_create(lbm_ctx* c, Slab& s, int rank, int device, const int* obst)
     d.aw2 = P.density * P.accel / 36.f;      // d2q9-bgk.c:238
     d.ll_in = s.ll_in; d.ll_up = d.ll_down = nullptr;
     d.rec = s.rec;
+    d.df_k = c->df_k;
     d.task_begin = s.sched + o_tb; d.n_interior = s.sched + o_ni; d.n_edge = s.sched + o_ne; d.task_order = (const int2*)(s.sched + o_to);
     d.dep_begin = s.sched + o_db; d.deps = s.sched + o_dp;
     d.flags = s.flags;
@@ -862,7 +875,8 @@ static int run_engine3(lbm_ctx* c, int iters)
     unsigned base = c->base;
     void* args[] = {(void*)&s.dev, (void*)&par0, (void*)&step0, (void*)&it, (void*)&base};
     // cooperative only for the co-residency guarantee: every warp polls its neighbours' records
-    CK(cudaLaunchCooperativeKernel(dataflow_fn(c->strict), dim3(s.plan.num_tasks), dim3(32), args, 0, s.stream));
+    const int blocks = (s.plan.num_tasks + c->df_k - 1) / c->df_k;
+    CK(cudaLaunchCooperativeKernel(dataflow_fn(c->strict, c->df_k > 1), dim3(blocks), dim3(32), args, 0, s.stream));
     CK(cudaEventRecord(s.ev_stop, s.stream));
     c->base += (unsigned)iters + 1u;
     if (iters & 1) c->par ^= 1;

@@ -42,6 +42,40 @@ def test_random_state_matches_oracle_bit_exact(lbm, oracle, engine, nx, ny, wall
     np.testing.assert_allclose(got_av, ref_tot * inv, rtol=AV_RTOL)
 
 
+@pytest.mark.parametrize("k", [2, 3, 8])
+@pytest.mark.parametrize("nx,ny,walls", [(128, 128, True), (132, 40, False), (4, 3, False), (1024, 9, True), (256, 37, False)])
+def test_dataflow_engine_several_tasks_per_warp_matches_oracle(lbm, oracle, monkeypatch, k, nx, ny, walls):
+    """Engine 3 with k consecutive tasks per warp (what lattices of 2369-4736 tasks get automatically, e.g.
+    1024x512), forced on small lattices so that the oracle can follow: bit-exact, including a ragged last warp."""
+    monkeypatch.setenv("LBM_DF_TASKS_PER_WARP", str(k))
+    mask, f0 = random_case(nx, ny, seed=nx * 77 + ny + k, walls=walls)
+    p = dict(nx=nx, ny=ny, density=0.1, accel=0.005, omega=1.85)
+    ref_f, ref_tot = oracle.run(nx, ny, 9, p["density"], p["accel"], p["omega"], mask, f=f0)
+    with make(lbm, p, mask, iters=9, engine=3) as lat:
+        lat.set_cells(f0)
+        lat.run(4)
+        lat.run(5)
+        got_f, got_av, inv = lat.cells(), lat.av_vels(), lat.inv_free_cells()
+    assert np.array_equal(got_f.view(np.uint32), ref_f.view(np.uint32)), "lattice differs from the oracle"
+    np.testing.assert_allclose(got_av, ref_tot * inv, rtol=AV_RTOL)
+
+
+def test_mid_size_lattice_dataflow_equals_persistent_engine(lbm):
+    """1024x512 (4096 tasks: two per warp, picked automatically) against engine 1 on the same lattice."""
+    p, mask, lines = load_grid("1024x1024")
+    p = dict(p, ny=512)
+    mask = np.ascontiguousarray(mask[:512])
+    mask[-1, :] = 1
+    outs = []
+    for engine in (0, 1):
+        with make(lbm, p, mask, iters=120, engine=engine) as lat:
+            lat.run(120)
+            outs.append((lat.cells(), lat.av_vels(), lat.describe()))
+    assert "dataflow" in outs[0][2] and "persistent" in outs[1][2]
+    assert np.array_equal(outs[0][0], outs[1][0])
+    np.testing.assert_allclose(outs[0][1], outs[1][1], rtol=1e-6)
+
+
 @pytest.mark.parametrize("grid,steps", [("128x128", 1000), ("128x256", 1000), ("256x256", 1000),
                                         ("1024x1024", 200), ("2048x1024", 100)])
 def test_short_runs_match_unmodified_reference(lbm, golden, grid, steps):
