@@ -433,10 +433,11 @@ int configure_engine(lbm_ctx* c, int device)
     const long long warps3 = (long long)occ3 * sms;
     const bool mem3 = tasks * std::max(c->prm.max_iters, 1) * (long long)sizeof(double) <= (2LL << 30);
     // a warp owns 1 task, or several consecutive ones when the lattice has more tasks than resident warps.
-    // Measured (profiles/r01_small_lattice.md): 2 per warp still beats engine 1 by 2.3x (1024x512), 4 per warp
-    // loses to it (1024x1024: 73 vs 98 GLUPS) - auto stops at 2; a forced engine 3 may go to 8.
+    // Measured (profiles/r01_small_lattice.md): 2 per warp beats engine 1 by 2.3x (1024x512), 3 per warp by 1.4x
+    // (1024x768: 82 vs 59 GLUPS), 4 per warp loses to it (1024x896: 74 vs 85, 1024x1024: 73 vs 98) - auto stops
+    // at 3; a forced engine 3 may go to 8.
     const int k_min = (int)((tasks + warps3 - 1) / std::max(warps3, 1LL));
-    const bool fits3 = c->size == 1 && k_min <= 2 && mem3;
+    const bool fits3 = c->size == 1 && k_min <= 3 && mem3;
     c->df_k = k_min;
     if (c->engine == 3) {
         const int k = std::max(k_min, env_int("LBM_DF_TASKS_PER_WARP", 1));
