@@ -304,18 +304,21 @@ std::vector<unsigned char> pack_mask(const int* obst, int nx, int ny, int row_st
 // D2H it asynchronously on their own stream into one of two pinned buffers and copy the previous
 // chunk out to the caller's memory meanwhile.  The pinned buffers live in a process-wide pool.
 struct Piece { void* dst; const void* src; size_t bytes; };
-constexpr size_t kChunkBytes = (size_t)4 << 20;
+constexpr size_t kChunkBytes = (size_t)2 << 20;   // pinning costs ~1 ms per MB (more with 8 ranks at once): keep the pool small
+constexpr int kChunksPerBlock = 8;                // 4 threads x 2 chunks, one cudaHostAlloc
 std::mutex g_pin_mutex;
 std::vector<void*> g_pin_pool;
 
 void* pin_acquire()
 {
-    {
-        std::lock_guard<std::mutex> g(g_pin_mutex);
-        if (!g_pin_pool.empty()) { void* p = g_pin_pool.back(); g_pin_pool.pop_back(); return p; }
+    std::lock_guard<std::mutex> g(g_pin_mutex);     // held across the allocation: concurrent workers share ONE block
+    if (g_pin_pool.empty()) {
+        void* p = nullptr;
+        if (cudaHostAlloc(&p, kChunkBytes * kChunksPerBlock, cudaHostAllocPortable) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+        for (int i = 0; i < kChunksPerBlock; ++i) g_pin_pool.push_back((char*)p + (size_t)i * kChunkBytes);
     }
-    void* p = nullptr;
-    if (cudaHostAlloc(&p, kChunkBytes, cudaHostAllocPortable) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    void* p = g_pin_pool.back();
+    g_pin_pool.pop_back();
     return p;
 }
 void pin_release(void* p)
