@@ -299,8 +299,8 @@ std::vector<unsigned char> pack_mask(const int* obst, int nx, int ny, int row_st
 
 // ---- large device -> host downloads (collate, d2q9-bgk.c:395-447) -------------------------------
 // A plain cudaMemcpy of hundreds of MB into fresh pageable memory runs at ~4 GB/s on the B200 boxes
-// (first-touch page faults and a single staging thread; bench.py e2e phase "download").  Large
-// downloads instead go through pinned staging chunks: a few host threads each take every nt-th chunk,
+// (first-touch page faults and a single staging thread; bench.py e2e phase "download").  Downloads of
+// 128 MB and more instead go through pinned staging chunks: a few host threads each take every nt-th chunk,
 // D2H it asynchronously on their own stream into one of two pinned buffers and copy the previous
 // chunk out to the caller's memory meanwhile.  The pinned buffers live in a process-wide pool.
 struct Piece { void* dst; const void* src; size_t bytes; };
@@ -339,7 +339,9 @@ int download(int device, cudaStream_t stream, const std::vector<Piece>& pieces)
     }
     int nt = (int)std::min<size_t>(4, chunks.size() / 4);
     if (const char* e = getenv("LBM_HOST_THREADS")) nt = std::min(nt, std::max(1, atoi(e)));
-    if (total < ((size_t)32 << 20) || nt < 1 || env_int("LBM_PLAIN_DOWNLOAD", 0)) {      // small: the plain path
+    // below 128 MB the plain copy wins once the one-off pinning of the staging block is counted (8 ranks x 75 MB at
+    // 8 GPUs: ~20 ms plain against ~10 ms + a first call of 60-130 ms)
+    if (total < ((size_t)128 << 20) || nt < 1 || env_int("LBM_PLAIN_DOWNLOAD", 0)) {
         for (const Piece& pc : pieces) CK(cudaMemcpyAsync(pc.dst, pc.src, pc.bytes, cudaMemcpyDeviceToHost, stream));
         CK(cudaStreamSynchronize(stream));
         return 0;

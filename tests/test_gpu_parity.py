@@ -157,7 +157,7 @@ def test_mass_conservation_and_obstacle_invariants_full_size(lbm, grid, steps):
 
 
 def test_pipelined_download_equals_plain_copy(lbm, monkeypatch):
-    """Downloads above 32 MB stream through pinned staging chunks on several host threads (collate,
+    """Downloads of 128 MB and more stream through pinned staging chunks on several host threads (collate,
     d2q9-bgk.c:395-447); the result must be byte-identical to a plain cudaMemcpy, for the 9 planes and
     for the 4 final-state fields, on a lattice whose planes are not a multiple of the 4 MB chunk."""
     p, mask, lines = load_grid("4096x1024")
@@ -172,7 +172,7 @@ def test_pipelined_download_equals_plain_copy(lbm, monkeypatch):
         f1, s1 = lat.cells(), lat.final_state()
         monkeypatch.setenv("LBM_HOST_THREADS", "1")
         f2 = lat.cells()
-    assert f0.nbytes > (32 << 20) and np.array_equal(f0, f1) and np.array_equal(f0, f2)
+    assert f0.nbytes > (128 << 20) and np.array_equal(f0, f1) and np.array_equal(f0, f2)
     for a, b in zip(s0, s1):
         assert np.array_equal(a, b)
     assert np.isfinite(f0).all() and len(np.unique(f0[:, ::7, ::13])) > 1000
