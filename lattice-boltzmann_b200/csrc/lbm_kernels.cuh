@@ -1,4 +1,5 @@
-// lbm_kernels.cuh - the warp-task update and the two timestep engines built on it.
+// lbm_kernels.cuh - the warp-task update and the three timestep engines built on it (1: persistent,
+// progress flags; 2: one launch per step; 3: dataflow over tagged records for small lattices).
 #pragma once
 #include "lbm_device.cuh"
 
