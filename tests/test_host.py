@@ -88,6 +88,25 @@ def test_host_setup_selfcheck(lbm, nx, ny, size):
             os.environ.pop("LBM_HOST_THREADS", None)
 
 
+def test_planner_selfcheck_random_shapes(lbm):
+    """Property test of the host planner over random lattices, slab counts and CTA budgets (hypothesis):
+    every task scheduled once, interior tasks self-contained, dependencies complete, edge tasks first."""
+    from hypothesis import given, settings, strategies as st
+    lib = lbm.load_library()
+
+    @settings(max_examples=1000, deadline=None, derandomize=True)
+    @given(st.integers(1, 700), st.integers(3, 260), st.integers(1, 8), st.integers(1, 420), st.sampled_from([16, 24, 40, 64]))
+    def check(nx4, ny, size, ctas, edge_weight):
+        size = min(size, ny)
+        os.environ["LBM_EDGE_WEIGHT_16"] = str(edge_weight)      # weight of a slab-edge task when the ranges are cut
+        assert lib.lbm_plan_selftest(4 * nx4, ny, size, ctas) == 0, (4 * nx4, ny, size, ctas, lib.lbm_last_error().decode())
+
+    try:
+        check()
+    finally:
+        os.environ.pop("LBM_EDGE_WEIGHT_16", None)
+
+
 def run_exe(*args, cwd=None):
     return subprocess.run([EXE, *args], capture_output=True, text=True, cwd=cwd)
 
