@@ -19,14 +19,6 @@ SlabShape allocate_rows(int ny, int size, int rank)
     return s;
 }
 
-int choose_ctas(int nx, int rows, int max_resident)
-{
-    const int tpr = (nx + kTaskCells - 1) / kTaskCells;
-    const int64_t tasks = (int64_t)tpr * rows;
-    int64_t g = std::min<int64_t>(max_resident, tasks);
-    return (int)std::max<int64_t>(g, 1);
-}
-
 int Layout::strip_of(int ch) const
 {
     int s = (int)((int64_t)ch * strips / tpr);

@@ -81,9 +81,6 @@ struct SlabPlan {
 // Throws std::runtime_error on impossible arguments.
 SlabPlan make_plan(int nx, int ny, int rank, int size, int ctas);
 
-// Number of persistent CTAs to use: min(max_resident, number of tasks), at least 1.
-int choose_ctas(int nx, int rows, int max_resident);
-
 // Self-check used by the tests: every task appears exactly once, interior tasks really have
 // all neighbours inside the CTA, every neighbour owner of a boundary task is in deps, edge tasks
 // lead the boundary tasks.  Returns "" or a description.
