@@ -1,7 +1,7 @@
 #!/usr/bin/env python3
 """Where do the persistent engine's CTAs wait?  Runs one grid under several env variants and prints
 device-timed GLUPS plus the per-CTA cycle split (dev tool, GPU box).
-    python tools/probe_sync.py --synthetic 16384x256 --ngpus 2 --variants "LBM_DYN=0;LBM_DYN=1"
+    python tools/probe_sync.py --synthetic 16384x256 --ngpus 2 --variants "LBM_EDGE_WEIGHT_16=16;LBM_EDGE_WEIGHT_16=24"
 """
 import argparse
 import importlib
@@ -21,7 +21,7 @@ def main():
     ap.add_argument("--steps", type=int, default=2000)
     ap.add_argument("--reps", type=int, default=2)
     ap.add_argument("--ngpus", type=int, default=1)
-    ap.add_argument("--variants", default="LBM_DYN=0;LBM_DYN=1")
+    ap.add_argument("--variants", default="LBM_ENGINE=0", help="semicolon-separated variants, each a comma-separated list of ENV=value")
     ap.add_argument("--profile", type=int, default=1)
     ap.add_argument("--threads", type=int, default=0)
     ap.add_argument("--dump", type=int, default=0)
