@@ -156,6 +156,25 @@ def test_mass_conservation_and_obstacle_invariants_full_size(lbm, grid, steps):
     assert np.all(np.isfinite(pr))
 
 
+@pytest.mark.parametrize("grid,steps,shift", [("256x256", 200, 5), ("1024x1024", 60, 37), ("4096x1024", 30, 130)])
+def test_x_translation_equivariance_full_size(lbm, grid, steps, shift):
+    """x is periodic (d2q9-bgk.c:288-289) and every cell runs the same arithmetic, so shifting the obstacles by
+    k columns must shift the whole lattice by k columns BIT FOR BIT - at shifts that are not multiples of a
+    lane's 4 cells or a task's 128 cells this moves every wall and the wrap column onto other lanes, tasks and
+    CTAs.  A size-independent property the oracle cannot check at these sizes in seconds; av_vels only to the
+    rounding of the regrouped sum."""
+    p, mask, lines = load_grid(grid)
+    with make(lbm, p, mask, lines, iters=steps) as a:
+        a.run(steps)
+        fa, ava = a.cells(), a.av_vels()
+    shifted = np.ascontiguousarray(np.roll(mask, shift, axis=1))
+    with make(lbm, p, shifted, lines, iters=steps) as b:
+        b.run(steps)
+        fb, avb = b.cells(), b.av_vels()
+    assert np.array_equal(np.roll(fb, -shift, axis=2), fa)
+    np.testing.assert_allclose(avb, ava, rtol=2e-6)
+
+
 def test_pipelined_download_equals_plain_copy(lbm, monkeypatch):
     """Downloads of 128 MB and more stream through pinned staging chunks on several host threads (collate,
     d2q9-bgk.c:395-447); the result must be byte-identical to a plain cudaMemcpy, for the 9 planes and

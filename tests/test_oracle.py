@@ -80,6 +80,18 @@ def test_oracle_invariants(oracle):
     assert np.array_equal(fa[:, ny - 2][:, mask[ny - 2] == 1], f0[:, ny - 2][:, mask[ny - 2] == 1])
 
 
+@pytest.mark.parametrize("grid,steps,shift", [("128x256", 60, 3), ("256x256", 40, 5)])
+def test_oracle_x_translation_equivariance(oracle, grid, steps, shift):
+    """The property the GPU suite uses at full size (test_x_translation_equivariance_full_size), pinned on the
+    oracle first: shifting the obstacles by k columns shifts the lattice by k columns bit for bit."""
+    p, mask, _ = load_grid(grid)
+    fa, ta = oracle.run(p["nx"], p["ny"], steps, p["density"], p["accel"], p["omega"], mask)
+    shifted = np.ascontiguousarray(np.roll(mask, shift, axis=1))
+    fb, tb = oracle.run(p["nx"], p["ny"], steps, p["density"], p["accel"], p["omega"], shifted)
+    assert np.array_equal(np.roll(fb, -shift, axis=2), fa)
+    np.testing.assert_allclose(tb, ta, rtol=1e-5)        # sequential fp32 sums in a different cell order
+
+
 def test_inputs_match_generator_and_reference_if_present():
     import subprocess, sys
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
