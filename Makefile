@@ -21,7 +21,7 @@ all: $(EXE)
 $(LIB): $(PKG)/csrc/lbm_api.cu $(PKG)/csrc/lbm_plan.cpp $(PKG)/csrc/lbm_kernels.cuh $(PKG)/csrc/lbm_device.cuh $(PKG)/csrc/lbm_plan.hpp include/lbm_b200.h
 	$(NVCC) $(NVFLAGS) -shared $(PKG)/csrc/lbm_api.cu $(PKG)/csrc/lbm_plan.cpp -o $@
 
-$(EXE): src/d2q9-bgk.c include/lbm_b200.h $(LIB)
+$(EXE): src/d2q9-bgk.c src/fmt_e12.h include/lbm_b200.h $(LIB)
 	$(CC) $(CFLAGS) src/d2q9-bgk.c -L$(PKG) -llbm_b200 -Wl,-rpath,'$$ORIGIN/$(PKG)' -lm -o $@
 
 oracle:

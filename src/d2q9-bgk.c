@@ -19,16 +19,21 @@
  *                  -DDEBUG): one timestep per launch, printing "==timestep: t==", the step's
  *                  un-normalised sum of |u| and the total density (the conservation invariant)
  */
+#define _POSIX_C_SOURCE 200809L      /* pwrite */
+#include <fcntl.h>
 #include <math.h>
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
 #include <sys/time.h>
+#include <sys/types.h>
+#include <unistd.h>
 #ifdef _OPENMP
 #include <omp.h>
 #endif
 
 #include "../include/lbm_b200.h"
+#include "fmt_e12.h"
 
 #define FINALSTATEFILE "final_state.dat"
 #define AVVELSFILE "av_vels.dat"
@@ -111,12 +116,14 @@ static int* read_obstacles(const char* obstaclefile, const run_params* p, int* l
 }
 
 /* final_state.dat: "%d %d %.12E %.12E %.12E %.12E %d\n" per cell, jj outer / ii inner (:710-741).
- * Rows are formatted by all host threads into per-block buffers and written in order. */
+ * All host threads format blocks of rows into their own buffers (exact integer formatter, fmt_e12.h); the
+ * block lengths are scanned and every thread then writes its block at its own file offset (pwrite), so
+ * neither the formatting nor the copy into the page cache is serial. */
 static void write_final_state(const run_params* p, const int* mask, const float* ux, const float* uy,
                               const float* u, const float* pr)
 {
-    FILE* fp = fopen(FINALSTATEFILE, "w");
-    if (fp == NULL) die("could not open file output file", __LINE__, __FILE__);
+    const int fd = open(FINALSTATEFILE, O_WRONLY | O_CREAT | O_TRUNC, 0666);
+    if (fd < 0) die("could not open file output file", __LINE__, __FILE__);
     const int nx = p->nx, ny = p->ny;
     const size_t per_line = 2 * 11 + 4 * 20 + 8;           /* generous upper bound */
     int block = (int)((8u << 20) / (per_line * (size_t)nx));   /* ~8 MB of text per block */
@@ -128,11 +135,14 @@ static void write_final_state(const run_params* p, const int* mask, const float*
     const int group = block * nthreads;
     char** bufs = (char**)malloc(sizeof(char*) * nthreads);
     size_t* lens = (size_t*)malloc(sizeof(size_t) * nthreads);
-    if (!bufs || !lens) die("cannot allocate output buffers", __LINE__, __FILE__);
+    long long* offs = (long long*)malloc(sizeof(long long) * nthreads);
+    int* failed = (int*)calloc((size_t)nthreads, sizeof(int));
+    if (!bufs || !lens || !offs || !failed) die("cannot allocate output buffers", __LINE__, __FILE__);
     for (int t = 0; t < nthreads; t++) {
         bufs[t] = (char*)malloc(per_line * (size_t)nx * block);
         if (!bufs[t]) die("cannot allocate output buffers", __LINE__, __FILE__);
     }
+    long long file_off = 0;
     for (int j0 = 0; j0 < ny; j0 += group) {
 #ifdef _OPENMP
 #pragma omp parallel for schedule(static, 1)
@@ -144,25 +154,52 @@ static void write_final_state(const run_params* p, const int* mask, const float*
             for (int jj = ja; jj < jb; jj++) {
                 for (int ii = 0; ii < nx; ii++) {
                     const size_t c = (size_t)jj * nx + ii;
-                    w += sprintf(w, "%d %d %.12E %.12E %.12E %.12E %d\n", ii, jj, ux[c], uy[c], u[c], pr[c], mask[c]);
+                    w = fmt_int(w, ii); *w++ = ' ';
+                    w = fmt_int(w, jj); *w++ = ' ';
+                    w = fmt_e12(w, ux[c]); *w++ = ' ';
+                    w = fmt_e12(w, uy[c]); *w++ = ' ';
+                    w = fmt_e12(w, u[c]); *w++ = ' ';
+                    w = fmt_e12(w, pr[c]); *w++ = ' ';
+                    w = fmt_int(w, mask[c]); *w++ = '\n';
                 }
             }
             lens[t] = (ja < ny) ? (size_t)(w - bufs[t]) : 0;
         }
+        for (int t = 0; t < nthreads; t++) { offs[t] = file_off; file_off += (long long)lens[t]; }
+#ifdef _OPENMP
+#pragma omp parallel for schedule(static, 1)
+#endif
+        for (int t = 0; t < nthreads; t++) {
+            size_t done = 0;
+            while (done < lens[t]) {
+                const ssize_t k = pwrite(fd, bufs[t] + done, lens[t] - done, (off_t)(offs[t] + (long long)done));
+                if (k <= 0) { failed[t] = 1; break; }
+                done += (size_t)k;
+            }
+        }
         for (int t = 0; t < nthreads; t++)
-            if (lens[t] && fwrite(bufs[t], 1, lens[t], fp) != lens[t]) die("could not write output file", __LINE__, __FILE__);
+            if (failed[t]) die("could not write output file", __LINE__, __FILE__);
     }
     for (int t = 0; t < nthreads; t++) free(bufs[t]);
     free(bufs);
     free(lens);
-    fclose(fp);
+    free(offs);
+    free(failed);
+    if (close(fd) != 0) die("could not write output file", __LINE__, __FILE__);
 }
 
 static void write_av_vels(const run_params* p, const float* av_vels)
 {
     FILE* fp = fopen(AVVELSFILE, "w");
     if (fp == NULL) die("could not open file output file", __LINE__, __FILE__);
-    for (int ii = 0; ii < p->max_iters; ii++) fprintf(fp, "%d:\t%.12E\n", ii, av_vels[ii]);
+    char line[64];
+    for (int ii = 0; ii < p->max_iters; ii++) {          /* "%d:\t%.12E\n" (:747) */
+        char* w = fmt_int(line, ii);
+        *w++ = ':'; *w++ = '\t';
+        w = fmt_e12(w, av_vels[ii]);
+        *w++ = '\n';
+        if (fwrite(line, 1, (size_t)(w - line), fp) != (size_t)(w - line)) die("could not write output file", __LINE__, __FILE__);
+    }
     fclose(fp);
 }
 

@@ -107,6 +107,30 @@ def test_planner_selfcheck_random_shapes(lbm):
         os.environ.pop("LBM_EDGE_WEIGHT_16", None)
 
 
+def test_exact_text_formatter_matches_printf(tmp_path):
+    """src/fmt_e12.h (the integer-arithmetic "%.12E" / "%d" used for final_state.dat and av_vels.dat) against
+    snprintf byte for byte: special values, every binade's edges, values that round across a power of ten,
+    4 M random bit patterns over all exponents and 4 M in the LBM range (tests/fmt_check.c)."""
+    exe = tmp_path / "fmt_check"
+    subprocess.run(["gcc", "-O2", "-std=gnu99", "-Wall", os.path.join(ROOT, "tests", "fmt_check.c"), "-o", str(exe)], check=True)
+    r = subprocess.run([str(exe), "4"], capture_output=True, text=True)
+    assert r.returncode == 0 and " 0 mismatches" in r.stdout, r.stdout[-2000:]
+
+
+@pytest.mark.parametrize("nx,ny,threads", [(260, 37, "8"), (4, 3, "1"), (16384, 9, "5"), (132, 700, "3")])
+def test_driver_writers_byte_identical_to_reference_formats(tmp_path, nx, ny, threads):
+    """The host driver's own write_final_state() / write_av_vels() (compiled in from src/d2q9-bgk.c) on a
+    synthetic lattice with zeros, negative zeros, tiny and ordinary values: files byte-identical to the
+    reference's fprintf formats (d2q9-bgk.c:739, 747), whatever the thread count (tests/cli_writer_check.c)."""
+    exe = tmp_path / "writer_check"
+    pkg = os.path.join(ROOT, "lattice-boltzmann_b200")
+    subprocess.run(["gcc", "-std=c99", "-Wall", "-O2", "-fopenmp", os.path.join(ROOT, "tests", "cli_writer_check.c"),
+                    "-L" + pkg, "-llbm_b200", "-Wl,-rpath," + pkg, "-lm", "-o", str(exe)], check=True)
+    r = subprocess.run([str(exe), str(nx), str(ny)], capture_output=True, text=True, cwd=tmp_path,
+                       env=dict(os.environ, OMP_NUM_THREADS=threads))
+    assert r.returncode == 0 and "writers identical" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
+
+
 def run_exe(*args, cwd=None):
     return subprocess.run([EXE, *args], capture_output=True, text=True, cwd=cwd)
 
