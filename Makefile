@@ -27,10 +27,18 @@ $(EXE): src/d2q9-bgk.c src/fmt_e12.h include/lbm_b200.h $(LIB)
 oracle:
 	$(MAKE) -C oracle
 
-check:
+# the known answers are regenerated from the committed fixtures (tests/golden/shipped_*.npz) on first use
+$(REF_FINAL_STATE_FILE) $(REF_AV_VELS_FILE):
+	python tools/make_check_files.py
+
+check: $(REF_FINAL_STATE_FILE) $(REF_AV_VELS_FILE)
 	python $(CHECKER) --ref-av-vels-file=$(REF_AV_VELS_FILE) --ref-final-state-file=$(REF_FINAL_STATE_FILE) --av-vels-file=$(AV_VELS_FILE) --final-state-file=$(FINAL_STATE_FILE)
 
-.PHONY: all check clean oracle
+# compute-sanitizer over the small grids, every engine (GPU box): see tools/sanitize.sh
+sanitize: all
+	bash tools/sanitize.sh
+
+.PHONY: all check clean oracle sanitize
 
 clean:
 	rm -f $(EXE) $(LIB)

@@ -55,10 +55,13 @@ typedef struct lbm_options {
                            2 = fast: FMA contraction allowed (within check.py's tolerance) */
     int ctas_per_sm;    /* 0 = auto */
     int threads_per_cta;/* 0 = auto (multiple of 32) */
-    int engine;         /* 0 = auto (3 where it applies, else 1); 1 = persistent neighbour-synchronised
-                           kernel; 2 = one launch per timestep (CUDA-graph replayed); 3 = dataflow over
-                           tagged records: one resident warp per 128-cell task, single lattices of at
-                           most ~2300 tasks (128x128 ... 512x512) */
+    int engine;         /* 0 = auto (4 or 3 where they apply, else 1); 1 = persistent neighbour-synchronised
+                           kernel; 2 = one launch per timestep (CUDA-graph replayed, single slab); 3 = dataflow
+                           over tagged records: one resident warp per 128-cell task (or per 2-3 of them), slabs
+                           of at most ~7000 tasks (... 512x512, 1024x768); 4 = the same with 32-cell tasks, one
+                           cell per lane: slabs of at most ~4700 such tasks (128x128 ... 256x256), nx % 32 == 0.
+                           Engines 3 and 4 also run row slabs on several GPUs (records of the edge rows are
+                           stored straight into the ring neighbour's record lattice). */
     int first_device;   /* first CUDA device ordinal used (single-process multi-GPU uses
                            first_device .. first_device+ngpus-1) */
 } lbm_options;
@@ -75,7 +78,8 @@ typedef struct lbm_options {
 int lbm_create(lbm_ctx** out, const lbm_params* params, const int* obstacles, int ngpus,
                const lbm_options* opts);
 
-/* Frees everything (finalise(), d2q9-bgk.c:656-673).  NULL is allowed. */
+/* Frees everything (finalise(), d2q9-bgk.c:656-673).  NULL is allowed.  Waits for every slab's enqueued
+ * work first, so it is safe straight after lbm_run.  One-process-per-GPU mode: see lbm_rank_disconnect. */
 void lbm_destroy(lbm_ctx* ctx);
 
 /* ---- the hot path ------------------------------------------------------------ */
@@ -174,6 +178,15 @@ int lbm_host_selftest(int nx, int ny, int size, long long seed);
  * differ in any bit from the IEEE-rounded intrinsics.  *mismatches must come back 0. */
 int lbm_selftest_math(long long n, long long seed, long long* mismatches);
 
+/* Device stress test of the tagged 16-byte records that carry the halos between GPUs (and the whole lattice
+ * of engines 3 and 4): a kernel on `writer_device` rewrites 16 K records living on `reader_device` with
+ * {t,t,t,t}, t = 1..rounds, through the product's store (one scalar st.relaxed.sys.b128) while a kernel on
+ * `reader_device` keeps reading them through the product's read path (mode 0: ld.relaxed.sys.b128; mode 1: the
+ * 16-byte cp.async into shared memory used by the halo staging).  *torn = records seen with mixed words (must be
+ * 0), *changes = times a record changed between two consecutive looks (> 0 proves the kernels overlapped).
+ * writer_device == reader_device runs both kernels side by side on one GPU. */
+int lbm_selftest_records(int writer_device, int reader_device, int rounds, int mode, long long* torn, long long* changes);
+
 /* ---- one process per GPU (torchrun-style launch) -------------------------------
  * Rank r of `size` owns slab r on CUDA device `device`.  After creation every rank
  * exports an opaque blob (the CUDA IPC handle of its inbound halo slots), the
@@ -186,6 +199,12 @@ int lbm_create_rank(lbm_ctx** out, const lbm_params* params, const int* obstacle
                     int rank, int size, int device, const lbm_options* opts);
 int lbm_rank_export(lbm_ctx* ctx, void* blob /* LBM_IPC_BLOB_BYTES */);
 int lbm_rank_connect(lbm_ctx* ctx, const void* blob_up, const void* blob_down);
+/* Teardown order in this mode (CUDA IPC requires importers to unmap before the exporter frees):
+ *   every rank: lbm_rank_disconnect (waits for the local kernel, unmaps the neighbours' slots);
+ *   host barrier across the ranks;  every rank: lbm_destroy.
+ * No kernel can still be writing into a slab at that point: a slab whose own kernel has finished has consumed
+ * every halo record a neighbour will send it (the last timestep of a run pushes nothing). */
+int lbm_rank_disconnect(lbm_ctx* ctx);
 /* 1/free_cells by the rule of params.obstacle_lines (for the caller's final scaling). */
 float lbm_inv_free_cells(const lbm_ctx* ctx);
 

@@ -71,10 +71,12 @@ SYMBOLS = {
     "lbm_plan_selftest": (ctypes.c_int, [ctypes.c_int] * 4),
     "lbm_host_selftest": (ctypes.c_int, [ctypes.c_int] * 3 + [ctypes.c_longlong]),
     "lbm_selftest_math": (ctypes.c_int, [ctypes.c_longlong, ctypes.c_longlong, ctypes.POINTER(ctypes.c_longlong)]),
+    "lbm_selftest_records": (ctypes.c_int, [ctypes.c_int] * 4 + [ctypes.POINTER(ctypes.c_longlong)] * 2),
     "lbm_create_rank": (ctypes.c_int, [ctypes.POINTER(_P), ctypes.POINTER(Params), _P, ctypes.c_int, ctypes.c_int,
                                        ctypes.c_int, ctypes.POINTER(Options)]),
     "lbm_rank_export": (ctypes.c_int, [_P, _P]),
     "lbm_rank_connect": (ctypes.c_int, [_P, _P, _P]),
+    "lbm_rank_disconnect": (ctypes.c_int, [_P]),
     "lbm_inv_free_cells": (ctypes.c_float, [_P]),
 }
 
@@ -116,6 +118,16 @@ def selftest_math(n=1 << 26, seed=1):
     if lib.lbm_selftest_math(n, seed, ctypes.byref(bad)):
         raise LbmError(_err(lib))
     return bad.value
+
+
+def selftest_records(writer_device=0, reader_device=0, rounds=2000, mode=0):
+    """(torn, changes): torn 16-byte records seen (must be 0) and value changes observed between consecutive
+    looks (> 0: reads and writes overlapped) while one kernel rewrites tagged records and another reads them."""
+    lib = load_library()
+    torn, changes = ctypes.c_longlong(-1), ctypes.c_longlong(-1)
+    if lib.lbm_selftest_records(writer_device, reader_device, rounds, mode, ctypes.byref(torn), ctypes.byref(changes)):
+        raise LbmError(_err(lib))
+    return torn.value, changes.value
 
 
 def device_count():
@@ -204,8 +216,11 @@ class Lattice:
         self._ck(self.lib.lbm_get_tot_u(self._ctx, out.ctypes.data, first, n))
         return out
 
-    def cells(self):
-        f = np.empty((NSPEEDS, self.rows, self.nx), np.float32)
+    def cells(self, out=None):
+        """The nine planes of this context's rows (collate's cells_global, d2q9-bgk.c:397-443); `out` = a
+        caller-owned float32 array (9, rows, nx) to fill instead of a fresh one (e.g. long-lived pinned memory)."""
+        f = np.empty((NSPEEDS, self.rows, self.nx), np.float32) if out is None else out
+        assert f.shape == (NSPEEDS, self.rows, self.nx) and f.dtype == np.float32 and f.flags.c_contiguous
         self._ck(self.lib.lbm_get_cells(self._ctx, _planes(f)))
         return f
 
@@ -286,6 +301,10 @@ class Lattice:
 
     def rank_connect(self, blob_up, blob_down):
         self._ck(self.lib.lbm_rank_connect(self._ctx, blob_up, blob_down))
+
+    def rank_disconnect(self):
+        """Unmaps the neighbours' halo slots; every rank calls it, then a host barrier, then close()."""
+        self._ck(self.lib.lbm_rank_disconnect(self._ctx))
 
 
 def read_params(path):

@@ -62,11 +62,13 @@ struct Slab {
     cudaGraphExec_t graph = nullptr;
     int graph_steps = 0;
     int graph_par = -1;
-    uint4* rec = nullptr;          // engine 3: the lattice as tagged records [parity 2][row][group 3][plane 4][nx/4]
+    uint4* rec = nullptr;          // engines 3 / 4: the lattice as tagged records [parity 2][haloed row][group 3][nx]
     uint4* ll_in = nullptr;        // inbound halo slots [parity 2][side 2][record 4][nx/4] (multi-slab only)
     // IPC (one-process-per-GPU mode): the ring neighbours' inbound halo slots
     void* ipc_ll_up = nullptr;
     void* ipc_ll_down = nullptr;
+    void* ipc_rec_up = nullptr;    // dataflow engines across processes: the neighbours' record lattices
+    void* ipc_rec_down = nullptr;
     int finalized_steps = 0;       // partials already folded into tot
 };
 
@@ -228,6 +230,49 @@ __global__ void k_selftest_math(unsigned long long n, unsigned long long seed, i
     if (local) atomicAdd(bad, local);
 }
 
+
+// ---- torn-record stress test (lbm_selftest_records) ---------------------------------------------------
+// Writer: every thread rewrites its records with {t,t,t,t} for t = 1..rounds through st_record, the product's
+// store, at full rate.  Reader (other GPU over NVLink, or other SMs of the same GPU): sweeps the same records
+// through the product's two read paths - ld_record (mode 0) and the cp.async 16-byte copy into shared memory used
+// by the halo staging (mode 1) - and counts records whose four words are not all equal (TORN) and how many
+// times a record's value changed between two looks (proof that reads and writes really overlapped).  Neither
+// kernel waits for the other, so nothing can hang.
+__global__ void k_records_writer(uint4* slots, int n, unsigned rounds)
+{
+    for (unsigned t = 1; t <= rounds; ++t)
+        for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+            lbm::st_record(slots + i, __uint_as_float(t), __uint_as_float(t), __uint_as_float(t), t);
+}
+
+__global__ void k_records_reader(const uint4* slots, int n, int sweeps, int mode, unsigned long long* out /* torn, changes */)
+{
+    __shared__ uint4 stage[256];
+    unsigned long long torn = 0, changes = 0;
+    const int i0 = blockIdx.x * blockDim.x + threadIdx.x, stride = gridDim.x * blockDim.x;
+    for (int sw = 0; sw < sweeps; ++sw) {
+        unsigned last = 0xffffffffu;
+        for (int i = i0; i < n; i += stride) {
+            for (int rep = 0; rep < 4; ++rep) {       // look at the same record a few times in a row
+                uint4 v;
+                if (mode == 0) {
+                    v = lbm::ld_record(slots + i);
+                } else {
+                    lbm::cp_async_record(stage + threadIdx.x, slots + i);
+                    lbm::cp_async_commit();
+                    asm volatile("cp.async.wait_group 0;" ::: "memory");
+                    v = stage[threadIdx.x];
+                }
+                if (v.x != v.w || v.y != v.w || v.z != v.w) ++torn;
+                if (rep && v.w != last) ++changes;
+                last = v.w;
+            }
+        }
+    }
+    if (torn) atomicAdd(out, torn);
+    if (changes) atomicAdd(out + 1, changes);
+}
+
 }  // namespace
 
 // =========================================================================== slab set-up
@@ -242,10 +287,18 @@ const void* persistent_pick(bool strict, bool ring)
     return strict ? (const void*)lbm::lbm_persistent_kernel<true, false, PROF> : (const void*)lbm::lbm_persistent_kernel<false, false, PROF>;
 }
 
-const void* dataflow_fn(bool strict, bool multi)
+template <bool RING>
+const void* dataflow_pick(bool strict, bool multi)
 {
-    if (multi) return strict ? (const void*)lbm::lbm_dataflow_kernel<true, true> : (const void*)lbm::lbm_dataflow_kernel<false, true>;
-    return strict ? (const void*)lbm::lbm_dataflow_kernel<true, false> : (const void*)lbm::lbm_dataflow_kernel<false, false>;
+    if (multi) return strict ? (const void*)lbm::lbm_dataflow_kernel<true, true, RING> : (const void*)lbm::lbm_dataflow_kernel<false, true, RING>;
+    return strict ? (const void*)lbm::lbm_dataflow_kernel<true, false, RING> : (const void*)lbm::lbm_dataflow_kernel<false, false, RING>;
+}
+const void* dataflow_fn(bool strict, bool multi, bool ring) { return ring ? dataflow_pick<true>(strict, multi) : dataflow_pick<false>(strict, multi); }
+
+const void* narrow_fn(bool strict, bool ring)
+{
+    if (ring) return strict ? (const void*)lbm::lbm_narrow_kernel<true, true> : (const void*)lbm::lbm_narrow_kernel<false, true>;
+    return strict ? (const void*)lbm::lbm_narrow_kernel<true, false> : (const void*)lbm::lbm_narrow_kernel<false, false>;
 }
 
 // LBM_PROFILE=1 selects the instantiations that carry the per-warp cycle counters
@@ -397,6 +450,8 @@ void slab_free(Slab& s)
     if (s.graph) cudaGraphExecDestroy(s.graph);
     if (s.ipc_ll_up) cudaIpcCloseMemHandle(s.ipc_ll_up);
     if (s.ipc_ll_down && s.ipc_ll_down != s.ipc_ll_up) cudaIpcCloseMemHandle(s.ipc_ll_down);
+    if (s.ipc_rec_up) cudaIpcCloseMemHandle(s.ipc_rec_up);
+    if (s.ipc_rec_down && s.ipc_rec_down != s.ipc_rec_up) cudaIpcCloseMemHandle(s.ipc_rec_down);
     const double t1 = now();
     cudaFree(s.buf[0]);
     const double t2 = now();
@@ -427,31 +482,45 @@ int configure_engine(lbm_ctx* c, int device)
     c->strict = (c->opt.strict_fp != 2);
     if (env_int("LBM_FAST_FP", 0)) c->strict = false;
     c->engine = c->opt.engine ? c->opt.engine : env_int("LBM_ENGINE", 0);
-    if (c->engine < 0 || c->engine > 3) return fail("unknown engine %d", c->engine);
+    if (c->engine < 0 || c->engine > 4) return fail("unknown engine %d", c->engine);
     if (c->engine == 2 && c->size > 1) return fail("engine 2 (launch per timestep) supports a single slab only");
-    if (c->engine == 3 && c->size > 1) return fail("engine 3 (dataflow over tagged records) supports a single slab only");
-    // engine 3 needs every warp-task on its own resident warp (one warp per block) and keeps one partial
-    // sum per task and step; auto picks it whenever the lattice is small enough for both
-    const long long tasks = (long long)((c->prm.nx + lbm::kTaskCells - 1) / lbm::kTaskCells) * c->prm.ny;
-    int occ3 = 0;
-    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ3, dataflow_fn(c->strict, false), 32, 0));
-    const long long warps3 = (long long)occ3 * sms;
-    const bool mem3 = tasks * std::max(c->prm.max_iters, 1) * (long long)sizeof(double) <= (2LL << 30);
-    // a warp owns 1 task, or several consecutive ones when the lattice has more tasks than resident warps.
+    // The dataflow engines (3: 128-cell tasks, 4: 32-cell tasks) need every task of a slab on its own resident
+    // warp (one warp per block) and keep one partial sum per task and step; auto picks them whenever the slab
+    // is small enough for both.  Every rank must decide alike, so the decision uses the LARGEST slab of the ring
+    // (rank 0's: ceil(ny / size) rows).
+    const bool ring = c->size > 1;
+    const int rows_max = (c->prm.ny + c->size - 1) / c->size;
+    const long long tasks = (long long)((c->prm.nx + lbm::kTaskCells - 1) / lbm::kTaskCells) * rows_max;
+    const long long ntasks = (c->prm.nx % 32 == 0) ? (long long)(c->prm.nx / 32) * rows_max : -1;
+    // resident warps: the smaller of the two instantiations' occupancies, so that whichever is launched
+    // (one task per warp, or several) passes the cooperative launch's co-residency check
+    int occ3 = 0, occ3m = 0, occ4 = 0;
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ3, dataflow_fn(c->strict, false, ring), 32, 0));
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ3m, dataflow_fn(c->strict, true, ring), 32, 0));
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ4, narrow_fn(c->strict, ring), 32, 0));
+    const long long warps3 = (long long)std::min(occ3, occ3m) * sms, warps4 = (long long)occ4 * sms;
+    const long long steps = std::max(c->prm.max_iters, 1);
+    const bool mem3 = tasks * steps * (long long)sizeof(double) <= (2LL << 30);
+    const bool mem4 = ntasks * steps * (long long)sizeof(double) <= (2LL << 30);
+    const bool fits4 = ntasks > 0 && ntasks <= warps4 && mem4;
+    // engine 3: a warp owns 1 task, or several consecutive ones when the slab has more tasks than resident warps.
     // Measured (profiles/r01_small_lattice.md): 2 per warp beats engine 1 by 2.3x (1024x512), 3 per warp by 1.4x
     // (1024x768: 82 vs 59 GLUPS), 4 per warp loses to it (1024x896: 74 vs 85, 1024x1024: 73 vs 98) - auto stops
     // at 3; a forced engine 3 may go to 8.
     const int k_min = (int)((tasks + warps3 - 1) / std::max(warps3, 1LL));
-    const bool fits3 = c->size == 1 && k_min <= 3 && mem3;
+    const bool fits3 = k_min <= 3 && mem3;
     c->df_k = k_min;
     if (c->engine == 3) {
         const int k = std::max(k_min, env_int("LBM_DF_TASKS_PER_WARP", 1));
-        if (c->size != 1 || !mem3 || k > 8)
-            return fail("engine 3 needs a single lattice of at most %lld warp-tasks (this one has %lld) and at most 2 GiB of "
+        if (!mem3 || k > 8)
+            return fail("engine 3 needs slabs of at most %lld warp-tasks (the largest here has %lld) and at most 2 GiB of "
                         "per-step partial sums", 8 * warps3, tasks);
         c->df_k = k;
     }
-    if (c->engine == 0) c->engine = fits3 ? 3 : 1;
+    if (c->engine == 4 && !fits4)
+        return fail("engine 4 (one cell per lane) needs nx %% 32 == 0, slabs of at most %lld 32-cell tasks (the largest here "
+                    "has %lld) and at most 2 GiB of per-step partial sums", warps4, ntasks);
+    if (c->engine == 0) c->engine = fits4 ? 4 : fits3 ? 3 : 1;
     c->threads = c->opt.threads_per_cta ? c->opt.threads_per_cta : env_int("LBM_THREADS", 256);
     if (c->threads % 32 || c->threads < 32 || c->threads > 512) return fail("threads_per_cta must be a multiple of 32 in [32,512]");
     int per_sm = c->opt.ctas_per_sm ? c->opt.ctas_per_sm : env_int("LBM_CTAS_PER_SM", 2);
@@ -463,9 +532,9 @@ int configure_engine(lbm_ctx* c, int device)
     if (occ < 1) return fail("persistent kernel does not fit on an SM with %d threads", c->threads);
     per_sm = std::max(1, std::min(per_sm, occ));
     c->ctas_budget = sms * per_sm;
-    if (c->engine == 3) {                // one block of one warp per task
+    if (c->engine == 3 || c->engine == 4) {      // one block of one warp per task (engine 3: or per df_k tasks)
         c->threads = 32;
-        c->ctas_budget = (int)tasks;
+        c->ctas_budget = (int)tasks;             // the plan keeps one "CTA" per wide task; engine 4 sizes its own partials
         return 0;
     }
     const int cap = env_int("LBM_MAX_CTAS", 0);
@@ -492,7 +561,8 @@ int slab_create(lbm_ctx* c, Slab& s, int rank, int device, const int* obst)
     if (9 * ps >= (1LL << 32))
         return fail("slab of %d rows x %d cells is too large for 32-bit lattice offsets (9*(rows+2)*nx must be < 2^32); "
                     "use more GPUs", pl.rows, P.nx);
-    const int G = pl.num_ctas;
+    // slots of per-step partial sums: one per persistent CTA (engine 1), per wide task (3) or per narrow task (4)
+    const int G = (c->engine == 4) ? pl.rows * (P.nx / 32) : pl.num_ctas;
     const int pitch = ((P.nx + 7) / 8 + 15) / 16 * 16;
 
     for (int i = 0; i < 2; ++i) CK(cudaMalloc(&s.buf[i], sizeof(float) * 9 * ps));
@@ -508,8 +578,8 @@ int slab_create(lbm_ctx* c, Slab& s, int rank, int device, const int* obst)
         CK(cudaMalloc(&s.ll_in, sizeof(uint4) * 4 * (size_t)P.nx));
         CK(cudaMemsetAsync(s.ll_in, 0, sizeof(uint4) * 4 * (size_t)P.nx, s.stream));
     }
-    if (c->engine == 3) {  // tag 0 = never written
-        const size_t bytes = sizeof(uint4) * 2 * 3 * (size_t)pl.rows * P.nx;
+    if (c->engine == 3 || c->engine == 4) {  // tag 0 = never written
+        const size_t bytes = sizeof(uint4) * 2 * 3 * (size_t)(pl.rows + 2) * P.nx;
         CK(cudaMalloc(&s.rec, bytes));
         CK(cudaMemsetAsync(s.rec, 0, bytes, s.stream));
     }
@@ -551,7 +621,7 @@ int slab_create(lbm_ctx* c, Slab& s, int rank, int device, const int* obst)
     d.aw1 = P.density * P.accel / 9.f;       // d2q9-bgk.c:237
     d.aw2 = P.density * P.accel / 36.f;      // d2q9-bgk.c:238
     d.ll_in = s.ll_in; d.ll_up = d.ll_down = nullptr;
-    d.rec = s.rec;
+    d.rec = s.rec; d.rec_up = d.rec_down = nullptr; d.rows_up = d.rows_down = 0;
     d.df_k = c->df_k;
     d.task_begin = s.sched + o_tb; d.n_interior = s.sched + o_ni; d.n_edge = s.sched + o_ne; d.task_order = (const int2*)(s.sched + o_to);
     d.dep_begin = s.sched + o_db; d.deps = s.sched + o_dp;
@@ -601,7 +671,8 @@ void describe(lbm_ctx* c)
     const Slab& s = c->slabs[0];
     snprintf(c->desc, sizeof(c->desc),
              "engine=%s fp=%s slabs=%d/%d ctas/slab=%d threads/cta=%d tasks/slab=%d tasks/row=%d strips=%d interior=%.0f%%",
-             c->engine == 1 ? "persistent-neighbour-sync" : c->engine == 3 ? "dataflow-tagged-records" : "launch-per-step-graph",
+             c->engine == 1 ? "persistent-neighbour-sync" : c->engine == 3 ? "dataflow-tagged-records"
+             : c->engine == 4 ? "narrow-dataflow-one-cell-per-lane" : "launch-per-step-graph",
              c->strict ? "strict" : "fast",
              c->nslabs, c->size, s.plan.num_ctas, c->threads, s.plan.num_tasks, s.plan.tpr, s.plan.strips,
              100.0 * lbm::interior_fraction(s.plan));
@@ -697,9 +768,65 @@ int lbm_selftest_math(long long n, long long seed, long long* mismatches)
     return 0;
 }
 
+int lbm_selftest_records(int writer_device, int reader_device, int rounds, int mode, long long* torn, long long* changes)
+{
+    if (!torn || !changes || rounds < 1 || mode < 0 || mode > 1) return fail("bad arguments");
+    const int ndev = lbm_device_count();
+    if (writer_device < 0 || reader_device < 0 || writer_device >= ndev || reader_device >= ndev)
+        return fail("lbm_selftest_records: devices %d / %d but %d visible", writer_device, reader_device, ndev);
+    const int n = 64 * 256;                              // 256 KB of records, the size of a 16384-wide slab's inbound slots
+    uint4* slots = nullptr;
+    unsigned long long* out = nullptr;
+    cudaStream_t sw = nullptr, sr = nullptr;
+    CK(cudaSetDevice(reader_device));                    // the slots live with the reader, as the halo slots do
+    CK(cudaMalloc(&slots, sizeof(uint4) * n));
+    CK(cudaMemset(slots, 0, sizeof(uint4) * n));
+    CK(cudaMalloc(&out, 2 * sizeof(unsigned long long)));
+    CK(cudaMemset(out, 0, 2 * sizeof(unsigned long long)));
+    CK(cudaStreamCreateWithFlags(&sr, cudaStreamNonBlocking));
+    CK(cudaDeviceSynchronize());
+    if (writer_device != reader_device) {
+        int can = 0;
+        CK(cudaDeviceCanAccessPeer(&can, writer_device, reader_device));
+        if (!can) return fail("device %d cannot access peer %d", writer_device, reader_device);
+        CK(cudaSetDevice(writer_device));
+        cudaError_t e = cudaDeviceEnablePeerAccess(reader_device, 0);
+        if (e == cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError();
+        else if (e != cudaSuccess) return fail("cudaDeviceEnablePeerAccess: %s", cudaGetErrorString(e));
+    }
+    CK(cudaSetDevice(writer_device));
+    CK(cudaStreamCreateWithFlags(&sw, cudaStreamNonBlocking));
+    // 64 CTAs each: on one GPU both kernels fit side by side (148 SMs), so they overlap there as well
+    k_records_writer<<<64, 256, 0, sw>>>(slots, n, (unsigned)rounds);
+    CK(cudaGetLastError());
+    CK(cudaSetDevice(reader_device));
+    k_records_reader<<<64, 256, 0, sr>>>(slots, n, std::max(1, rounds / 4), mode, out);
+    CK(cudaGetLastError());
+    CK(cudaStreamSynchronize(sr));
+    CK(cudaSetDevice(writer_device));
+    CK(cudaStreamSynchronize(sw));
+    unsigned long long h[2] = {0, 0};
+    CK(cudaSetDevice(reader_device));
+    CK(cudaMemcpy(h, out, sizeof(h), cudaMemcpyDeviceToHost));
+    CK(cudaFree(slots));
+    CK(cudaFree(out));
+    CK(cudaStreamDestroy(sr));
+    CK(cudaSetDevice(writer_device));
+    CK(cudaStreamDestroy(sw));
+    *torn = (long long)h[0];
+    *changes = (long long)h[1];
+    return 0;
+}
+
 void lbm_destroy(lbm_ctx* c)
 {
     if (!c) return;
+    // Every slab's kernel must have finished before ANY slab's memory goes: a ring neighbour pushes halo
+    // records into this slab's inbound slots until its second-to-last step.  (Once a slab's own kernel has
+    // finished it has consumed every record it will ever be sent - the last step pushes nothing - so in
+    // one-process-per-GPU mode this local synchronisation is all the teardown needs.)
+    for (Slab& s : c->slabs)
+        if (s.stream) { cudaSetDevice(s.device); cudaStreamSynchronize(s.stream); }
     for (Slab& s : c->slabs) slab_free(s);
     delete c;
 }
@@ -765,6 +892,8 @@ int lbm_create(lbm_ctx** out, const lbm_params* params, const int* obstacles, in
         }
         s.dev.ll_up = up.ll_in;
         s.dev.ll_down = dn.ll_in;
+        s.dev.rec_up = up.rec;     s.dev.rows_up = up.plan.rows;
+        s.dev.rec_down = dn.rec;   s.dev.rows_down = dn.plan.rows;
     }
     if (rc) { lbm_destroy(c); return 1; }
     c->connected = true;
@@ -872,21 +1001,30 @@ static int run_engine2(lbm_ctx* c, int iters)
     return 0;
 }
 
-static int run_engine3(lbm_ctx* c, int iters)
+// engines 3 and 4: one cooperative launch per slab (cooperative only for the co-residency guarantee: every warp
+// polls its neighbours' records)
+static int run_dataflow(lbm_ctx* c, int iters)
 {
-    Slab& s = c->slabs[0];
-    CK(cudaSetDevice(s.device));
-    CK(cudaEventRecord(s.ev_start, s.stream));
-    int par0 = c->par, step0 = c->steps_done, it = iters;
-    unsigned base = c->base;
-    void* args[] = {(void*)&s.dev, (void*)&par0, (void*)&step0, (void*)&it, (void*)&base};
-    // cooperative only for the co-residency guarantee: every warp polls its neighbours' records
-    const int blocks = (s.plan.num_tasks + c->df_k - 1) / c->df_k;
-    CK(cudaLaunchCooperativeKernel(dataflow_fn(c->strict, c->df_k > 1), dim3(blocks), dim3(32), args, 0, s.stream));
-    CK(cudaEventRecord(s.ev_stop, s.stream));
+    const bool ring = c->size > 1;
+    int launches = 0;
+    for (Slab& s : c->slabs) {
+        CK(cudaSetDevice(s.device));
+        CK(cudaEventRecord(s.ev_start, s.stream));
+        int par0 = c->par, step0 = c->steps_done, it = iters;
+        unsigned base = c->base;
+        void* args[] = {(void*)&s.dev, (void*)&par0, (void*)&step0, (void*)&it, (void*)&base};
+        if (c->engine == 4) {
+            CK(cudaLaunchCooperativeKernel(narrow_fn(c->strict, ring), dim3(s.plan.rows * (c->prm.nx / 32)), dim3(32), args, 0, s.stream));
+        } else {
+            const int blocks = (s.plan.num_tasks + c->df_k - 1) / c->df_k;
+            CK(cudaLaunchCooperativeKernel(dataflow_fn(c->strict, c->df_k > 1, ring), dim3(blocks), dim3(32), args, 0, s.stream));
+        }
+        CK(cudaEventRecord(s.ev_stop, s.stream));
+        ++launches;
+    }
     c->base += (unsigned)iters + 1u;
     if (iters & 1) c->par ^= 1;
-    c->last_launches = 1;
+    c->last_launches = launches;
     return 0;
 }
 
@@ -918,7 +1056,7 @@ int lbm_run(lbm_ctx* c, int iters)
     if (c->steps_done + iters > c->prm.max_iters)
         return fail("lbm_run: %d + %d steps exceed max_iters=%d", c->steps_done, iters, c->prm.max_iters);
     if (c->size > 1 && !c->connected) return fail("lbm_run: ring neighbours not connected (call lbm_rank_connect)");
-    const int rc = (c->engine == 1) ? run_engine1(c, iters) : (c->engine == 3) ? run_engine3(c, iters) : run_engine2(c, iters);
+    const int rc = (c->engine == 1) ? run_engine1(c, iters) : (c->engine == 2) ? run_engine2(c, iters) : run_dataflow(c, iters);
     if (rc) return rc;
     c->steps_done += iters;
     return 0;
@@ -964,7 +1102,7 @@ int fold_partials(lbm_ctx* c, Slab& s)
     if (c->engine == 2 || s.finalized_steps >= c->steps_done) return 0;
     CK(cudaSetDevice(s.device));
     const int n = c->steps_done - s.finalized_steps;
-    k_fold_partials<<<(n + 7) / 8, 256, 0, s.stream>>>(s.partials, s.tot, s.plan.num_ctas, s.finalized_steps, c->steps_done);
+    k_fold_partials<<<(n + 7) / 8, 256, 0, s.stream>>>(s.partials, s.tot, s.dev.num_ctas, s.finalized_steps, c->steps_done);
     CK(cudaGetLastError());
     s.finalized_steps = c->steps_done;
     return 0;
@@ -1124,8 +1262,9 @@ int lbm_total_density(lbm_ctx* c, float* out)
 // Blob layout: magic, rank, size, nx, then the IPC handle of the slab's inbound halo slots.
 struct IpcBlob {
     unsigned magic;
-    int rank, size, nx;
-    cudaIpcMemHandle_t ll_in;
+    int rank, size, nx, rows, engine;
+    cudaIpcMemHandle_t ll_in;      // engine 1: inbound halo slots
+    cudaIpcMemHandle_t rec;        // engines 3 / 4: the record lattice (its two haloed rows are written by the neighbours)
 };
 static_assert(sizeof(IpcBlob) <= LBM_IPC_BLOB_BYTES, "IPC blob too large");
 
@@ -1158,8 +1297,9 @@ int lbm_rank_export(lbm_ctx* c, void* blob)
     IpcBlob b;
     memset(&b, 0, sizeof(b));
     b.magic = 0x4C424D32u;  // "LBM2"
-    b.rank = c->rank0; b.size = c->size; b.nx = c->prm.nx;
+    b.rank = c->rank0; b.size = c->size; b.nx = c->prm.nx; b.rows = s.plan.rows; b.engine = c->engine;
     if (c->size > 1) CK(cudaIpcGetMemHandle(&b.ll_in, s.ll_in));
+    if (c->size > 1 && s.rec) CK(cudaIpcGetMemHandle(&b.rec, s.rec));
     memset(blob, 0, LBM_IPC_BLOB_BYTES);
     memcpy(blob, &b, sizeof(b));
     return 0;
@@ -1180,13 +1320,39 @@ int lbm_rank_connect(lbm_ctx* c, const void* blob_up, const void* blob_down)
     if (up.rank != r_up || dn.rank != r_dn || up.size != c->size || dn.size != c->size)
         return fail("lbm_rank_connect: blobs are from ranks %d/%d, expected up=%d down=%d", up.rank, dn.rank, r_up, r_dn);
     if (up.nx != c->prm.nx || dn.nx != c->prm.nx) return fail("lbm_rank_connect: neighbour lattice width differs");
+    if (up.engine != c->engine || dn.engine != c->engine)
+        return fail("lbm_rank_connect: neighbours run engines %d / %d, this rank engine %d", up.engine, dn.engine, c->engine);
     const bool same = (r_up == r_dn);   // size == 2: both neighbours are the same process
     CK(cudaIpcOpenMemHandle(&s.ipc_ll_up, up.ll_in, cudaIpcMemLazyEnablePeerAccess));
     if (same) s.ipc_ll_down = s.ipc_ll_up;
     else CK(cudaIpcOpenMemHandle(&s.ipc_ll_down, dn.ll_in, cudaIpcMemLazyEnablePeerAccess));
     s.dev.ll_up = (uint4*)s.ipc_ll_up;
     s.dev.ll_down = (uint4*)s.ipc_ll_down;
+    if (s.rec) {
+        CK(cudaIpcOpenMemHandle(&s.ipc_rec_up, up.rec, cudaIpcMemLazyEnablePeerAccess));
+        if (same) s.ipc_rec_down = s.ipc_rec_up;
+        else CK(cudaIpcOpenMemHandle(&s.ipc_rec_down, dn.rec, cudaIpcMemLazyEnablePeerAccess));
+        s.dev.rec_up = (uint4*)s.ipc_rec_up;     s.dev.rows_up = up.rows;
+        s.dev.rec_down = (uint4*)s.ipc_rec_down; s.dev.rows_down = dn.rows;
+    }
     c->connected = true;
+    return 0;
+}
+
+int lbm_rank_disconnect(lbm_ctx* c)
+{
+    if (!c || !c->rank_mode) return fail("lbm_rank_disconnect: needs a context made by lbm_create_rank");
+    if (c->size == 1 || !c->connected) return 0;
+    if (lbm_sync(c)) return 1;                       // my kernel may still be pushing into the mappings
+    Slab& s = c->slabs[0];
+    CK(cudaSetDevice(s.device));
+    if (s.ipc_ll_up) CK(cudaIpcCloseMemHandle(s.ipc_ll_up));
+    if (s.ipc_ll_down && s.ipc_ll_down != s.ipc_ll_up) CK(cudaIpcCloseMemHandle(s.ipc_ll_down));
+    if (s.ipc_rec_up) CK(cudaIpcCloseMemHandle(s.ipc_rec_up));
+    if (s.ipc_rec_down && s.ipc_rec_down != s.ipc_rec_up) CK(cudaIpcCloseMemHandle(s.ipc_rec_down));
+    s.ipc_ll_up = s.ipc_ll_down = s.ipc_rec_up = s.ipc_rec_down = nullptr;
+    s.dev.ll_up = s.dev.ll_down = s.dev.rec_up = s.dev.rec_down = nullptr;
+    c->connected = false;
     return 0;
 }
 

@@ -146,8 +146,8 @@ __device__ __forceinline__ bool ll_take(const uint4* stage, const TaskGeom& g, i
 }
 
 // Updates the 4 cells of this lane for one task: pull (propagate), rebound / collision,
-// optional accelerate_flow epilogue for the NEXT step on row ny-2, store, halo push to the ring
-// neighbours, and returns the lane's sum of |u| over its fluid cells.  On a slab edge row the row
+// accelerate_flow epilogue for the NEXT step on row ny-2 and halo push to the ring neighbours (both only
+// when a next step follows in this run: `epilogue_accel`), store, and returns the lane's sum of |u| over its fluid cells.  On a slab edge row the row
 // beyond the edge is pulled from the inbound halo slots, which must carry `tag`; pushes carry tag + 1.
 template <bool S, bool RING>
 __device__ __forceinline__ float process_task(const SlabDev& d, int par, int2 td, int lane, bool epilogue_accel, unsigned tag,
@@ -242,11 +242,14 @@ __device__ __forceinline__ float process_task(const SlabDev& d, int par, int2 td
 #pragma unroll
         for (int k = 0; k < 9; ++k) st_cg4(dst + ((unsigned)k * ps + g.rc), o[k]);
         // halo push over NVLink: only the three populations that cross the slab edge, as tagged
-        // records into the ring neighbour's inbound slots of the other parity
+        // records into the ring neighbour's inbound slots of the other parity.  The last step of a run
+        // pushes nothing (the next run's prologue republishes the edge rows): a slab whose kernel has
+        // finished has therefore consumed every record a neighbour will ever send it, so nothing can
+        // still be in flight towards its memory when the host frees it (lbm_destroy).
         const int Q = d.nx >> 2, q = g.x0 >> 2;
-        if (ll_n)            // my top row -> the up neighbour's side 0 (row below its first row)
+        if (ll_n && epilogue_accel)   // my top row -> the up neighbour's side 0 (row below its first row)
             st_halo(d.ll_up + ll_slot(d, par ^ 1, 0) + q, Q, o[2], o[5], o[6], tag + 1u);
-        if (ll_s)            // my bottom row -> the down neighbour's side 1 (row above its last row)
+        if (ll_s && epilogue_accel)   // my bottom row -> the down neighbour's side 1 (row above its last row)
             st_halo(d.ll_down + ll_slot(d, par ^ 1, 1) + q, Q, o[4], o[7], o[8], tag + 1u);
     } else {
         usum = 0.f;
@@ -467,13 +470,37 @@ __global__ void __launch_bounds__(512, 1) lbm_persistent_kernel(SlabDev d, int p
 // The SoA lattice stays the canonical state BETWEEN runs: the prologue converts the warp's own row
 // segment into records (after the in-place accelerate_flow of the first step), the last step stores
 // SoA.  Per step every warp leaves its own partial sum of |u| (partials[step][task], folded later in a
-// fixed order).  Single lattice only.
+// fixed order).
+// Row slabs on several GPUs (RING): the record lattice has one haloed row either side, exactly like the
+// SoA lattice; the top row's northbound group is stored straight into the up neighbour's haloed row 0 and
+// the bottom row's southbound group into the down neighbour's last haloed row, through peer pointers -
+// the consumer still polls only its own memory, and the cross-GPU hop needs nothing beyond the records
+// themselves (this is engine 1's halo-slot protocol applied to every row).  This is the few-rows-per-GPU
+// path: a 1024x1024 lattice on 8 GPUs is 1024 resident warps per GPU.
 // ------------------------------------------------------------------------------------------
 constexpr int kRecNorthbound = 0, kRecSouthbound = 1, kRecHorizontal = 2;
 
-__device__ __forceinline__ uint4* rec_group(const SlabDev& d, int par, int row, int kind)
+// Record group `kind` of haloed row `hrow` (local row r = haloed row r + 1) in a record lattice of `rows` real rows.
+__device__ __forceinline__ uint4* rec_group_at(uint4* base, int rows, int nx, int par, int hrow, int kind)
 {
-    return d.rec + ((size_t)(par * d.rows + row) * 3 + kind) * (size_t)d.nx;
+    return base + ((size_t)(par * (rows + 2) + hrow) * 3 + kind) * (size_t)nx;
+}
+__device__ __forceinline__ uint4* rec_group(const SlabDev& d, int par, int hrow, int kind)
+{
+    return rec_group_at(d.rec, d.rows, d.nx, par, hrow, kind);
+}
+// Where local row lr's groups are READ from / WRITTEN to.  Single lattice: y wraps inside the slab.
+template <bool RING> __device__ __forceinline__ int rec_hrow_south(const SlabDev& d, int lr) { return lr == 0 ? (RING ? 0 : d.rows) : lr; }
+template <bool RING> __device__ __forceinline__ int rec_hrow_north(const SlabDev& d, int lr) { return lr == d.rows - 1 ? (RING ? d.rows + 1 : 1) : lr + 2; }
+template <bool RING> __device__ __forceinline__ uint4* rec_out_north(const SlabDev& d, int par, int lr)
+{
+    if (RING && lr == d.rows - 1) return rec_group_at(d.rec_up, d.rows_up, d.nx, par, 0, kRecNorthbound);
+    return rec_group(d, par, lr + 1, kRecNorthbound);
+}
+template <bool RING> __device__ __forceinline__ uint4* rec_out_south(const SlabDev& d, int par, int lr)
+{
+    if (RING && lr == 0) return rec_group_at(d.rec_down, d.rows_down, d.nx, par, d.rows_down + 1, kRecSouthbound);
+    return rec_group(d, par, lr + 1, kRecSouthbound);
 }
 
 // One record group of this lane's 4 cells (+ the west / east element on the lanes that need one);
@@ -500,26 +527,28 @@ __device__ __forceinline__ bool rec_take(const SlabDev& d, const uint4* base, co
 // warp that owns several consecutive ids owns vertically adjacent rows of one chunk.
 struct DfTask {
     TaskGeom g;
-    int id, q, row_s, row_n;
+    int id, q, hrow_s, hrow_n;
     unsigned nib;
 };
 
+template <bool RING>
 __device__ __forceinline__ DfTask df_task(const SlabDev& d, int id, int lane)
 {
     DfTask t;
     t.id = id;
-    t.g = task_geom<false>(d, make_int2(id % d.rows, id / d.rows), lane);
+    t.g = task_geom<RING>(d, make_int2(id % d.rows, id / d.rows), lane);
     t.q = t.g.x0 >> 2;
-    t.row_s = t.g.lr == 0 ? d.rows - 1 : t.g.lr - 1;
-    t.row_n = t.g.lr == d.rows - 1 ? 0 : t.g.lr + 1;
+    t.hrow_s = rec_hrow_south<RING>(d, t.g.lr);
+    t.hrow_n = rec_hrow_north<RING>(d, t.g.lr);
     const unsigned mbyte = __ldg(d.mask + ((unsigned)(t.g.lr + 1) * (unsigned)d.mask_pitch + ((unsigned)t.g.xc >> 3)));
     t.nib = (mbyte >> (t.g.xc & 4)) & 0xFu;
     return t;
 }
 
-// Prologue of a run: the task's row segment of the SoA lattice -> records of parity 0, tag base + 1,
+// Prologue of a run: the task's row segment of the SoA lattice -> records of parity rp0 (= step0 & 1), tag base + 1,
 // after the in-place accelerate_flow of the first step (d2q9-bgk.c:235-266).
-__device__ __forceinline__ void df_prologue(const SlabDev& d, const DfTask& t, int par0, unsigned base)
+template <bool RING>
+__device__ __forceinline__ void df_prologue(const SlabDev& d, const DfTask& t, int par0, int rp0, unsigned base)
 {
     const TaskGeom& g = t.g;
     const int Q = d.nx >> 2;
@@ -538,14 +567,14 @@ __device__ __forceinline__ void df_prologue(const SlabDev& d, const DfTask& t, i
         for (int k = 0; k < 9; ++k) v[k] = make_float4(p[0][k], p[1][k], p[2][k], p[3][k]);
     }
     if (g.active) {
-        st_halo(rec_group(d, 0, g.lr, kRecNorthbound) + t.q, Q, v[2], v[5], v[6], base + 1u);
-        st_halo(rec_group(d, 0, g.lr, kRecSouthbound) + t.q, Q, v[4], v[7], v[8], base + 1u);
-        st_halo(rec_group(d, 0, g.lr, kRecHorizontal) + t.q, Q, v[0], v[1], v[3], base + 1u);
+        st_halo(rec_out_north<RING>(d, rp0, g.lr) + t.q, Q, v[2], v[5], v[6], base + 1u);
+        st_halo(rec_out_south<RING>(d, rp0, g.lr) + t.q, Q, v[4], v[7], v[8], base + 1u);
+        st_halo(rec_group(d, rp0, g.lr + 1, kRecHorizontal) + t.q, Q, v[0], v[1], v[3], base + 1u);
     }
 }
 
 // One timestep of one task; false = bail out (status set: a neighbour never arrived).
-template <bool S>
+template <bool S, bool RING>
 __device__ __forceinline__ bool df_step(const SlabDev& d, const DfTask& t, int lane, int s, int iters, int par0, int step0, unsigned base)
 {
     const TaskGeom& g = t.g;
@@ -553,16 +582,17 @@ __device__ __forceinline__ bool df_step(const SlabDev& d, const DfTask& t, int l
     const unsigned ps = (unsigned)d.ps;
     const unsigned full = 0xffffffffu;
     const unsigned tag = base + 1u + (unsigned)s;
-    const int rp = s & 1;
+    const int rp = (step0 + s) & 1;   // record parity continues across runs: the next run's prologue must not hit the
+                                      // parity a ring neighbour's last step may still be reading
     float4 cv[3], sv[3], nv[3];      // (f0,f1,f3) of the row; (f2,f5,f6) of the south row; (f4,f7,f8) of the north row
     float w1 = 0.f, w5 = 0.f, w8 = 0.f, e3 = 0.f, e6 = 0.f, e7 = 0.f;
     long long t0 = 0;
     // all loads of the three groups go out back to back and are voted on ONCE; polling the groups one by
     // one measured slower (three dependent votes on the fast path)
     for (int tries = 0;; ++tries) {
-        bool ok = rec_take<0>(d, rec_group(d, rp, g.lr, kRecHorizontal), g, tag, cv, w1, e3);
-        ok = rec_take<0>(d, rec_group(d, rp, t.row_s, kRecNorthbound), g, tag, sv, w5, e6) && ok;
-        ok = rec_take<1>(d, rec_group(d, rp, t.row_n, kRecSouthbound), g, tag, nv, w8, e7) && ok;
+        bool ok = rec_take<0>(d, rec_group(d, rp, g.lr + 1, kRecHorizontal), g, tag, cv, w1, e3);
+        ok = rec_take<0>(d, rec_group(d, rp, t.hrow_s, kRecNorthbound), g, tag, sv, w5, e6) && ok;
+        ok = rec_take<1>(d, rec_group(d, rp, t.hrow_n, kRecSouthbound), g, tag, nv, w8, e7) && ok;
         if (__all_sync(full, ok)) break;
         // give up warp-uniformly (another warp failed, or a neighbour never arrives)
         if (tries == 0) t0 = clock64();
@@ -602,9 +632,9 @@ __device__ __forceinline__ bool df_step(const SlabDev& d, const DfTask& t, int l
 #pragma unroll
         for (int k = 0; k < 9; ++k) o[k] = make_float4(p[0][k], p[1][k], p[2][k], p[3][k]);
         if (!last) {
-            st_halo(rec_group(d, rp ^ 1, g.lr, kRecNorthbound) + t.q, Q, o[2], o[5], o[6], tag + 1u);
-            st_halo(rec_group(d, rp ^ 1, g.lr, kRecSouthbound) + t.q, Q, o[4], o[7], o[8], tag + 1u);
-            st_halo(rec_group(d, rp ^ 1, g.lr, kRecHorizontal) + t.q, Q, o[0], o[1], o[3], tag + 1u);
+            st_halo(rec_out_north<RING>(d, rp ^ 1, g.lr) + t.q, Q, o[2], o[5], o[6], tag + 1u);
+            st_halo(rec_out_south<RING>(d, rp ^ 1, g.lr) + t.q, Q, o[4], o[7], o[8], tag + 1u);
+            st_halo(rec_group(d, rp ^ 1, g.lr + 1, kRecHorizontal) + t.q, Q, o[0], o[1], o[3], tag + 1u);
         } else {                                    // the run's result goes back to the SoA lattice
             float* dst = d.buf[par0 ^ (iters & 1)];
 #pragma unroll
@@ -621,7 +651,7 @@ __device__ __forceinline__ bool df_step(const SlabDev& d, const DfTask& t, int l
 // MULTI = false: one task per warp (block b owns task b).  MULTI = true: block b owns the df_k consecutive
 // tasks [b * df_k, ...), i.e. a column of vertically adjacent rows, and walks them in order every step
 // (a step-s task only ever waits for step s-1 outputs, so no cycle of waits can form).
-template <bool S, bool MULTI>
+template <bool S, bool MULTI, bool RING>
 __global__ void __launch_bounds__(32, 16) lbm_dataflow_kernel(SlabDev d, int par0, int step0, int iters, unsigned base)
 {
     const int lane = threadIdx.x;
@@ -629,17 +659,112 @@ __global__ void __launch_bounds__(32, 16) lbm_dataflow_kernel(SlabDev d, int par
         // block b = task (row b / tpr, chunk b % tpr): x-neighbours in adjacent blocks (measured: 256x256 1.68 us
         // per step against 1.85 with the chunk-major numbering of the multi-task mode)
         const int id = (blockIdx.x % d.tpr) * d.rows + blockIdx.x / d.tpr;
-        const DfTask t = df_task(d, id, lane);
-        df_prologue(d, t, par0, base);
+        const DfTask t = df_task<RING>(d, id, lane);
+        df_prologue<RING>(d, t, par0, step0 & 1, base);
         for (int s = 0; s < iters; ++s)
-            if (!df_step<S>(d, t, lane, s, iters, par0, step0, base)) return;
+            if (!df_step<S, RING>(d, t, lane, s, iters, par0, step0, base)) return;
     } else {
         const int first = blockIdx.x * d.df_k;
         const int n = min(d.df_k, d.rows * d.tpr - first);
-        for (int j = 0; j < n; ++j) df_prologue(d, df_task(d, first + j, lane), par0, base);
+        for (int j = 0; j < n; ++j) df_prologue<RING>(d, df_task<RING>(d, first + j, lane), par0, step0 & 1, base);
         for (int s = 0; s < iters; ++s)
             for (int j = 0; j < n; ++j)
-                if (!df_step<S>(d, df_task(d, first + j, lane), lane, s, iters, par0, step0, base)) return;
+                if (!df_step<S, RING>(d, df_task<RING>(d, first + j, lane), lane, s, iters, par0, step0, base)) return;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// Engine 4: narrow dataflow - ONE CELL PER LANE.  Same protocol as engine 3, but a task is 32 consecutive
+// cells of a row and a record {a,b,c,tag} holds the three populations of ONE cell of a group, so a lane's
+// whole input is three records (lanes 0 and 31 fetch three more for the cells west / east of the warp).
+// Why: on the check grids (128x128 ... 256x256) a timestep is one dependency chain - records visible in L2,
+// poll, collide, store - and a wide task puts ~950 instructions of ONE warp into it (four cells per lane,
+// issued by one scheduler).  With a quarter of the work per warp and four times the warps, the chain
+// carries ~300 instructions and the SM's four schedulers work on different tasks at once.  (A whole lattice
+// inside one thread-block cluster's shared memory - the other B200 option - is issue-bound instead: at most
+// 16 SMs for 128 tasks x 950 instructions = 1900 cycles per step at 4 IPC, no better than engine 3;
+// DSMEM latency, 215 cycles, is no shorter than an L2 hit, 234-262)
+// nx must be a multiple of 32; at most one task per resident warp (lbm_create falls back to engine 3 / 1).
+// ------------------------------------------------------------------------------------------
+template <bool S, bool RING>
+__global__ void __launch_bounds__(32, 24) lbm_narrow_kernel(SlabDev d, int par0, int step0, int iters, unsigned base)
+{
+    const unsigned full = 0xffffffffu;
+    const int lane = threadIdx.x;
+    const int tpr = d.nx >> 5;
+    const int lr = blockIdx.x / tpr, x = (blockIdx.x % tpr) * 32 + lane;
+    const int nx = d.nx;
+    const bool edge = (lane == 0) || (lane == 31);
+    const int xx = (lane == 0) ? (x == 0 ? nx - 1 : x - 1) : (x == nx - 1 ? 0 : x + 1);   // the cell beyond the warp (edge lanes)
+    const bool blocked = (__ldg(d.mask + ((unsigned)(lr + 1) * (unsigned)d.mask_pitch + ((unsigned)x >> 3))) >> (x & 7)) & 1u;
+    const bool accel_row = (lr == d.accel_lr);
+    const unsigned ps = (unsigned)d.ps;
+    const unsigned cell = (unsigned)(lr + 1) * (unsigned)nx + (unsigned)x;          // element offset in a SoA plane
+    const int hs = rec_hrow_south<RING>(d, lr), hn = rec_hrow_north<RING>(d, lr);
+
+    // ---- prologue: my cell of the SoA lattice -> records of parity step0 & 1 (after the first step's accelerate_flow)
+    {
+        const float* src = d.buf[par0];
+        float p[9];
+#pragma unroll
+        for (int k = 0; k < 9; ++k) p[k] = ld_cg1(src + ((unsigned)k * ps + cell));
+        if (accel_row) accelerate_cell(p, blocked, d.aw1, d.aw2);
+        const int rp0 = step0 & 1;
+        st_record(rec_out_north<RING>(d, rp0, lr) + x, p[2], p[5], p[6], base + 1u);
+        st_record(rec_out_south<RING>(d, rp0, lr) + x, p[4], p[7], p[8], base + 1u);
+        st_record(rec_group(d, rp0, lr + 1, kRecHorizontal) + x, p[0], p[1], p[3], base + 1u);
+    }
+
+    for (int s = 0; s < iters; ++s) {
+        const unsigned tag = base + 1u + (unsigned)s;
+        const int rp = (step0 + s) & 1;            // continues across runs (see df_step)
+        const uint4* gh = rec_group(d, rp, lr + 1, kRecHorizontal);
+        const uint4* gn = rec_group(d, rp, hs, kRecNorthbound);      // the south row's northbound populations
+        const uint4* gs = rec_group(d, rp, hn, kRecSouthbound);      // the north row's southbound populations
+        uint4 H, N, Sg, Hx, Nx, Sx;
+        Hx = Nx = Sx = make_uint4(0u, 0u, 0u, tag);
+        long long t0 = 0;
+        for (int tries = 0;; ++tries) {
+            H = ld_record(gh + x); N = ld_record(gn + x); Sg = ld_record(gs + x);
+            if (edge) { Hx = ld_record(gh + xx); Nx = ld_record(gn + xx); Sx = ld_record(gs + xx); }
+            const bool ok = H.w == tag && N.w == tag && Sg.w == tag && Hx.w == tag && Nx.w == tag && Sx.w == tag;
+            if (__all_sync(full, ok)) break;
+            if (tries == 0) t0 = clock64();
+            const bool late = clock64() - t0 > kSpinLimitCycles;
+            if (late) atomicExch(d.status, 2);
+            if (__any_sync(full, late || *(volatile int*)d.status != 0)) return;
+        }
+        // pull (d2q9-bgk.c:315): f1,f5,f8 come from the west cell, f3,f6,f7 from the east cell
+        float p[9];
+        p[0] = __uint_as_float(H.x);
+        p[2] = __uint_as_float(N.x);
+        p[4] = __uint_as_float(Sg.x);
+        const unsigned w1 = __shfl_up_sync(full, H.y, 1), w5 = __shfl_up_sync(full, N.y, 1), w8 = __shfl_up_sync(full, Sg.z, 1);
+        const unsigned e3 = __shfl_down_sync(full, H.z, 1), e6 = __shfl_down_sync(full, N.z, 1), e7 = __shfl_down_sync(full, Sg.y, 1);
+        p[1] = __uint_as_float(lane == 0 ? Hx.y : w1);
+        p[5] = __uint_as_float(lane == 0 ? Nx.y : w5);
+        p[8] = __uint_as_float(lane == 0 ? Sx.z : w8);
+        p[3] = __uint_as_float(lane == 31 ? Hx.z : e3);
+        p[6] = __uint_as_float(lane == 31 ? Nx.z : e6);
+        p[7] = __uint_as_float(lane == 31 ? Sx.y : e7);
+
+        float q[1][9];
+#pragma unroll
+        for (int k = 0; k < 9; ++k) q[0][k] = p[k];
+        const float usum = collide_n<S, 1>(q, blocked ? 1u : 0u, d.omega);
+        const bool last = (s + 1 == iters);
+        if (!last && accel_row) accelerate_cell(q[0], blocked, d.aw1, d.aw2);     // accelerate_flow for the next step
+        if (!last) {
+            st_record(rec_out_north<RING>(d, rp ^ 1, lr) + x, q[0][2], q[0][5], q[0][6], tag + 1u);
+            st_record(rec_out_south<RING>(d, rp ^ 1, lr) + x, q[0][4], q[0][7], q[0][8], tag + 1u);
+            st_record(rec_group(d, rp ^ 1, lr + 1, kRecHorizontal) + x, q[0][0], q[0][1], q[0][3], tag + 1u);
+        } else {                                    // the run's result goes back to the SoA lattice
+            float* dst = d.buf[par0 ^ (iters & 1)];
+#pragma unroll
+            for (int k = 0; k < 9; ++k) dst[(unsigned)k * ps + cell] = q[0][k];
+        }
+        const double acc = warp_sum((double)usum);
+        if (lane == 0) d.partials[(long long)(step0 + s) * d.num_ctas + blockIdx.x] = acc;
     }
 }
 

@@ -119,6 +119,8 @@ static int* read_obstacles(const char* obstaclefile, const run_params* p, int* l
  * All host threads format blocks of rows into their own buffers (exact integer formatter, fmt_e12.h); the
  * block lengths are scanned and every thread then writes its block at its own file offset (pwrite), so
  * neither the formatting nor the copy into the page cache is serial. */
+static double g_format_s = 0.0, g_pwrite_s = 0.0;     /* LBM_REPORT: where write_final_state's time went */
+
 static void write_final_state(const run_params* p, const int* mask, const float* ux, const float* uy,
                               const float* u, const float* pr)
 {
@@ -131,6 +133,7 @@ static void write_final_state(const run_params* p, const int* mask, const float*
     int nthreads = 1;
 #ifdef _OPENMP
     nthreads = omp_get_max_threads();
+    if (nthreads > 16) nthreads = 16;   /* 8 MB of text per thread; more writers only contend on the one file */
 #endif
     const int group = block * nthreads;
     char** bufs = (char**)malloc(sizeof(char*) * nthreads);
@@ -144,8 +147,9 @@ static void write_final_state(const run_params* p, const int* mask, const float*
     }
     long long file_off = 0;
     for (int j0 = 0; j0 < ny; j0 += group) {
+        const double t_a = wall();
 #ifdef _OPENMP
-#pragma omp parallel for schedule(static, 1)
+#pragma omp parallel for schedule(static, 1) num_threads(nthreads)
 #endif
         for (int t = 0; t < nthreads; t++) {
             char* w = bufs[t];
@@ -166,8 +170,9 @@ static void write_final_state(const run_params* p, const int* mask, const float*
             lens[t] = (ja < ny) ? (size_t)(w - bufs[t]) : 0;
         }
         for (int t = 0; t < nthreads; t++) { offs[t] = file_off; file_off += (long long)lens[t]; }
+        const double t_b = wall();
 #ifdef _OPENMP
-#pragma omp parallel for schedule(static, 1)
+#pragma omp parallel for schedule(static, 1) num_threads(nthreads)
 #endif
         for (int t = 0; t < nthreads; t++) {
             size_t done = 0;
@@ -179,6 +184,8 @@ static void write_final_state(const run_params* p, const int* mask, const float*
         }
         for (int t = 0; t < nthreads; t++)
             if (failed[t]) die("could not write output file", __LINE__, __FILE__);
+        g_format_s += t_b - t_a;
+        g_pwrite_s += wall() - t_b;
     }
     for (int t = 0; t < nthreads; t++) free(bufs[t]);
     free(bufs);
@@ -305,8 +312,13 @@ int main(int argc, char* argv[])
                 72.0 * updates / (ms * 1e-3) / 1e9 / slabs);
     }
 
+    const double out_tic = wall();
     write_final_state(&p, mask, fields, fields + n, fields + 2 * n, fields + 3 * n);
+    const double out_mid = wall();
     write_av_vels(&p, av_vels);
+    if (rep && atoi(rep))
+        fprintf(stderr, "output: final_state.dat %.3f s (format %.3f s, pwrite %.3f s), av_vels.dat %.3f s\n",
+                out_mid - out_tic, g_format_s, g_pwrite_s, wall() - out_mid);
 
     lbm_destroy(ctx);
     free(av_vels);

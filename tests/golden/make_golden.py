@@ -16,6 +16,13 @@ Nothing here runs on the GPU box; the .npz files it writes are committed.
   ref_short_<g>_<n>.npz  the same binary with maxIters cut to n: tight-tolerance target for the
                          CUDA path (fp32 rounding differences have no time to amplify).
 
+  ref_hash_<g>_<n>.json  BASELINE.json's large configurations (4096x1024, 8192x1024, 16384x1024 - the bench
+                         headline) and the periodic 128x256 grid, maxIters cut to n: SHA-256 of the fp32
+                         u_x / u_y / |u| / pressure planes the unmodified reference wrote, plus its av_vels
+                         values.  The planes are hundreds of MB, the fixture a few hundred bytes; the GPU
+                         test hashes lbm_get_final_state's output (bit-exact or nothing), bench.py's
+                         parity_check does the same at N > 1.  (--hashes-only makes just these.)
+
 Full runs take 15 s .. 15 min each; pass --cache DIR to reuse earlier outputs
 (DIR/<g>/{av_vels.dat,final_state.dat,stdout.txt}).
 """
@@ -38,6 +45,7 @@ SHORT = {"128x128": 1000, "128x256": 1000, "256x256": 1000, "1024x1024": 200, "2
 
 
 DEBUG_CASE = ("128x256", 25)
+HASHED = {"4096x1024": 20, "8192x1024": 20, "16384x1024": 20, "128x256": 200}
 
 
 def load_av(path):
@@ -95,13 +103,53 @@ def collect(g, d, fields):
     return out
 
 
+def plane_sha256(a):
+    import hashlib
+    return hashlib.sha256(np.ascontiguousarray(a, dtype="<f4").tobytes()).hexdigest()
+
+
+def hashes():
+    """ref_hash_<g>_<n>.json: see the module docstring.  final_state.dat of 16384x1024 is 1.4 GB of text:
+    parsed with pandas (float64, exact), then checked to be fp32-representable before hashing."""
+    import json
+    import pandas as pd
+    for g, n in HASHED.items():
+        nx, ny = (int(s) for s in g.split("x"))
+        with tempfile.TemporaryDirectory() as tmp:
+            run_ref(g, n, tmp)
+            fs = pd.read_csv(os.path.join(tmp, "final_state.dat"), sep=" ", header=None,
+                             names=["x", "y", "ux", "uy", "u", "pressure", "obst"], float_precision="round_trip")
+            av = f32_exact(load_av(os.path.join(tmp, "av_vels.dat")), g)
+            with open(os.path.join(tmp, "stdout.txt")) as fh:
+                re_line = re.search(r"Reynolds number:\s+(\S+)", fh.read()).group(1)
+        assert len(fs) == nx * ny and int(fs["x"].iloc[-1]) == nx - 1 and int(fs["y"].iloc[-1]) == ny - 1
+        out = {"grid": g, "steps": n, "made_by": "oracle/_ref/ref-serial (unmodified reference, gcc -O3)",
+               "dtype": "<f4, row-major [ny][nx]", "reynolds": re_line,
+               "av_vels": ["%.9e" % v for v in av.tolist()], "blocked_cells": int(fs["obst"].sum())}
+        for f in ("ux", "uy", "u", "pressure"):
+            a64 = fs[f].to_numpy()
+            a32 = f32_exact(a64, f"{g}.{f}")            # %.12E of the fp32 value == the printed text (sampled)
+            # ... and for every value: 13 printed digits pin the fp32 value (9 suffice), so the nearest
+            # fp32 must lie within the print rounding (half a unit of the 13th digit) of the text
+            if not np.all(np.abs(a32.astype(np.float64) - a64) <= 1e-12 * np.abs(a64)):
+                raise SystemExit(f"{g}.{f}: printed values are not fp32 values")
+            out["sha256_" + f] = plane_sha256(a32.reshape(ny, nx))
+        with open(os.path.join(HERE, f"ref_hash_{g}_{n}.json"), "w") as fh:
+            json.dump(out, fh, indent=1)
+        print("wrote ref_hash", g, n, out["sha256_pressure"][:16], flush=True)
+
+
 def main():
     ap = argparse.ArgumentParser()
+    ap.add_argument("--hashes-only", action="store_true", help="only the ref_hash_* fixtures of the large grids")
     ap.add_argument("--cache", help="directory with earlier full-length ref-serial outputs")
     ap.add_argument("--skip-full", action="store_true")
     args = ap.parse_args()
     if not (os.path.isdir(REF) and os.path.exists(REF_BIN)):
         raise SystemExit("needs /root/reference and oracle/_ref/ref-serial (run oracle/build_ref.sh)")
+    if args.hashes_only:
+        hashes()
+        return 0
     shipped()
     if not args.skip_full:
         for g in SHIPPED:
@@ -131,6 +179,7 @@ def main():
     with open(os.path.join(HERE, f"ref_debug_{g}_{n}.txt"), "w") as fh:
         fh.writelines(dbg)
     print("wrote ref_debug", g, n, len(dbg), "lines")
+    hashes()
     return 0
 
 

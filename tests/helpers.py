@@ -1,7 +1,32 @@
 """Shared helpers for the parity tests (test infrastructure)."""
+import hashlib
+import json
+import os
+
 import numpy as np
 
 import oracle_lib
+
+GOLDEN_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def plane_sha256(a):
+    """SHA-256 of a plane as little-endian fp32, row-major (how tests/golden/make_golden.py hashes
+    what the unmodified reference wrote)."""
+    return hashlib.sha256(np.ascontiguousarray(a, dtype="<f4").tobytes()).hexdigest()
+
+
+def load_ref_hash(grid, steps):
+    """tests/golden/ref_hash_<grid>_<steps>.json: hashes of the reference's final-state planes + its av_vels."""
+    with open(os.path.join(GOLDEN_DIR, f"ref_hash_{grid}_{steps}.json")) as fh:
+        g = json.load(fh)
+    g["av_vels"] = np.array([float(v) for v in g["av_vels"]], np.float32)
+    return g
+
+
+def assert_final_state_matches_ref_hash(g, ux, uy, u, pr):
+    for name, a in (("ux", ux), ("uy", uy), ("u", u), ("pressure", pr)):
+        assert plane_sha256(a) == g["sha256_" + name], f"{g['grid']}: {name} plane differs from the reference's"
 
 
 def load_grid(grid):

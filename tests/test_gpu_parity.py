@@ -12,7 +12,7 @@ additionally against the reference's shipped known answers at check.py's 1 %.
 import numpy as np
 import pytest
 
-from helpers import check_py_max_pcnt, load_grid, random_case
+from helpers import assert_final_state_matches_ref_hash, check_py_max_pcnt, load_grid, load_ref_hash, random_case
 
 pytestmark = pytest.mark.gpu
 
@@ -24,10 +24,14 @@ def make(lbm, p, mask, lines=-1, iters=None, **kw):
                        p["omega"], mask, obstacle_lines=lines, **kw)
 
 
-@pytest.mark.parametrize("engine", [1, 2, 3])
+@pytest.mark.parametrize("engine", [1, 2, 3, 4])
 @pytest.mark.parametrize("nx,ny,walls", [(128, 128, True), (128, 256, False), (256, 64, True), (132, 40, False),
-                                         (512, 16, False), (4, 3, False), (1024, 9, True)])
+                                         (512, 16, False), (4, 3, False), (1024, 9, True), (32, 5, False), (64, 3, True)])
 def test_random_state_matches_oracle_bit_exact(lbm, oracle, engine, nx, ny, walls):
+    if engine == 4 and nx % 32:
+        with pytest.raises(lbm.LbmError):       # one cell per lane needs whole 32-cell tasks; auto falls back
+            lbm.Lattice(nx, ny, 1, 0.1, 0.005, 1.85, np.zeros((ny, nx), np.int32), engine=4)
+        return
     mask, f0 = random_case(nx, ny, seed=nx * 1000 + ny, walls=walls)
     p = dict(nx=nx, ny=ny, density=0.1, accel=0.005, omega=1.85)
     iters = 7
@@ -71,7 +75,7 @@ def test_mid_size_lattice_dataflow_equals_persistent_engine(lbm):
         with make(lbm, p, mask, iters=120, engine=engine) as lat:
             lat.run(120)
             outs.append((lat.cells(), lat.av_vels(), lat.describe()))
-    assert "dataflow" in outs[0][2] and "persistent" in outs[1][2]
+    assert "dataflow-tagged" in outs[0][2] and "persistent" in outs[1][2]
     assert np.array_equal(outs[0][0], outs[1][0])
     np.testing.assert_allclose(outs[0][1], outs[1][1], rtol=1e-6)
 
@@ -88,6 +92,29 @@ def test_short_runs_match_unmodified_reference(lbm, golden, grid, steps):
     assert np.array_equal(pr, g["pressure"]) and np.array_equal(u, g["u"])
     if "ux" in g:
         assert np.array_equal(ux, g["ux"]) and np.array_equal(uy, g["uy"])
+    np.testing.assert_allclose(av, g["av_vels"], rtol=AV_RTOL)
+
+
+@pytest.mark.parametrize("grid,steps", [("128x256", 200), ("4096x1024", 20), ("8192x1024", 20), ("16384x1024", 20)])
+def test_large_baseline_configs_match_oracle_and_reference_bit_exact(lbm, oracle, grid, steps):
+    """BASELINE.json configs 4 and 5 at FULL size - 4096x1024, 8192x1024 and the bench headline 16384x1024
+    (reference: timestep, d2q9-bgk.c:268-339 on input_16384x1024.params) - on one GPU:
+      * all nine populations of every cell equal the oracle's bit for bit (the OpenMP oracle needs
+        about a second for 20 steps of 16.8 M cells), av_vels within AV_RTOL of its sequential fp32 sum;
+      * the four final-state planes hash to what the UNMODIFIED reference (oracle/_ref/ref-serial) wrote
+        for the same input (tests/golden/ref_hash_*.json, made by tests/golden/make_golden.py)."""
+    g = load_ref_hash(grid, steps)
+    p, mask, lines = load_grid(grid)
+    ref_f, ref_tot = oracle.run(p["nx"], p["ny"], steps, p["density"], p["accel"], p["omega"], mask)
+    with make(lbm, p, mask, lines, iters=steps) as lat:
+        lat.run(steps)
+        f = lat.cells()
+        fs = lat.final_state()
+        av = lat.av_vels()
+        inv = lat.inv_free_cells()
+    assert np.array_equal(f.view(np.uint32), ref_f.view(np.uint32)), "lattice differs from the oracle"
+    assert_final_state_matches_ref_hash(g, *fs)
+    np.testing.assert_allclose(av, ref_tot * inv, rtol=AV_RTOL)
     np.testing.assert_allclose(av, g["av_vels"], rtol=AV_RTOL)
 
 
@@ -118,7 +145,7 @@ def test_engines_and_split_runs_agree(lbm):
     p, mask, lines = load_grid("128x256")
     outs = []
     for engine, chunks in ((1, [300]), (2, [300]), (1, [1, 99, 64, 136]), (2, [150, 150]), (3, [300]), (3, [1, 99, 64, 136]),
-                           (0, [2, 298])):
+                           (4, [300]), (4, [1, 99, 63, 137]), (0, [2, 298])):
         with make(lbm, p, mask, lines, iters=300, engine=engine) as lat:
             for c in chunks:
                 lat.run(c)
@@ -289,24 +316,49 @@ def test_exact_division_and_sqrt_fast_paths(lbm, seed):
     assert lbm.selftest_math(1 << 28, seed) == 0
 
 
+@pytest.mark.parametrize("mode", [0, 1])
+def test_tagged_records_are_never_torn_one_gpu(lbm, mode):
+    """The halo slots and the record lattice of engines 3/4 rely on a 16-byte record {v,v,v,tag} being
+    written and read as ONE unit (st/ld.relaxed.sys.b128; mode 1: the 16-byte cp.async of the halo staging).
+    A writer kernel rewrites 16 K records at full rate while a reader kernel on other SMs keeps looking: no
+    record may ever show mixed words, and the reader must really have seen values change under it."""
+    torn, changes = lbm.selftest_records(0, 0, rounds=20000, mode=mode)
+    assert torn == 0
+    assert changes > 1000, "reader and writer did not overlap; the test proved nothing"
+
+
 def _ngpu(lbm):
     return lbm.device_count()
 
 
+@pytest.mark.parametrize("mode", [0, 1])
+def test_tagged_records_are_never_torn_over_nvlink(lbm, mode):
+    """The same with the writer on another GPU storing through a peer pointer (the halo push)."""
+    if _ngpu(lbm) < 2:
+        pytest.skip("needs 2 GPUs")
+    for w, r in ((1, 0), (0, 1)):
+        torn, changes = lbm.selftest_records(w, r, rounds=20000, mode=mode)
+        assert torn == 0
+        assert changes > 1000, "reader and writer did not overlap; the test proved nothing"
+
+
+@pytest.mark.parametrize("engine", [0, 1, 3])
 @pytest.mark.parametrize("ngpus", [2, 3, 4, 8])
 @pytest.mark.parametrize("grid,steps", [("128x256", 400), ("1024x1024", 150), ("128x128", 301)])
-def test_row_slabs_over_nvlink_equal_single_gpu(lbm, ngpus, grid, steps):
+def test_row_slabs_over_nvlink_equal_single_gpu(lbm, ngpus, grid, steps, engine):
     """Row decomposition over N GPUs (reference: allocate_rows + halo_exchange, d2q9-bgk.c:341-393,
     483-503), halos pushed over NVLink from inside the kernel: the lattice must equal the single-GPU
     lattice bit for bit (128x256 has periodic top/bottom, i.e. exercises the ring wrap link), and
-    av_vels must agree to the rounding of the final double->float conversion."""
+    av_vels must agree to the rounding of the final double->float conversion.  engine 0 = auto (the small grids
+    run the dataflow engines across GPUs: narrow tasks on 128-wide grids, several wide tasks per warp on
+    1024x1024), 1 = persistent kernel with halo slots, 3 = wide dataflow tasks."""
     if _ngpu(lbm) < ngpus:
         pytest.skip(f"needs {ngpus} GPUs")
     p, mask, lines = load_grid(grid)
-    with make(lbm, p, mask, lines, iters=steps) as one:
+    with make(lbm, p, mask, lines, iters=steps, engine=1) as one:
         one.run(steps)
         f1, av1 = one.cells(), one.av_vels()
-    with make(lbm, p, mask, lines, iters=steps, ngpus=ngpus) as many:
+    with make(lbm, p, mask, lines, iters=steps, ngpus=ngpus, engine=engine) as many:
         assert many.num_slabs() == ngpus
         many.run(steps // 3)
         many.run(steps - steps // 3)       # a second launch re-arms the neighbour flags
@@ -338,8 +390,9 @@ def test_baseline_slab_configs_equal_single_gpu(lbm, ngpus, grid, steps):
     assert abs(m1 - m0) / m0 < 1e-6 and abs(mn - m0) / m0 < 1e-6
 
 
+@pytest.mark.parametrize("engine", [0, 1, 3])
 @pytest.mark.parametrize("nx,ny,ngpus", [(256, 37, 2), (132, 5, 2), (256, 9, 4), (4, 3, 3), (256, 9, 8), (1024, 8, 8)])
-def test_slabs_random_state_matches_oracle(lbm, oracle, nx, ny, ngpus):
+def test_slabs_random_state_matches_oracle(lbm, oracle, nx, ny, ngpus, engine):
     """Random states on thin slabs (down to ONE row per GPU, where a task pulls both halo sides and the
     body-force row ny-2 is itself a slab edge row), ragged widths, no walls: bit-exact against the oracle,
     with set_cells between two launches (every launch republishes its edge rows)."""
@@ -348,7 +401,7 @@ def test_slabs_random_state_matches_oracle(lbm, oracle, nx, ny, ngpus):
     mask, f0 = random_case(nx, ny, seed=7 + nx + ny, walls=False)
     p = dict(nx=nx, ny=ny, density=0.1, accel=0.005, omega=1.85)
     ref_f, ref_tot = oracle.run(nx, ny, 9, p["density"], p["accel"], p["omega"], mask, f=f0)
-    with make(lbm, p, mask, iters=20, ngpus=ngpus) as lat:
+    with make(lbm, p, mask, iters=20, ngpus=ngpus, engine=engine) as lat:
         lat.run(4)                  # from the uniform initial state; discarded by set_cells
         lat.set_cells(f0)
         lat.run(5)
@@ -360,7 +413,7 @@ def test_slabs_random_state_matches_oracle(lbm, oracle, nx, ny, ngpus):
     np.testing.assert_allclose(av[4:13], ref_tot * inv, rtol=AV_RTOL)
 
 
-def _rank_worker(rank, size, port, grid, steps, out_dir):
+def _rank_worker(rank, size, port, grid, steps, out_dir, engine):
     """One process per GPU (the torchrun model): rank-mode lattice, blobs exchanged over gloo."""
     import importlib, os, sys
     import torch.distributed as dist
@@ -374,7 +427,7 @@ def _rank_worker(rank, size, port, grid, steps, out_dir):
     dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=size)
     p, mask, lines = load_grid(grid)
     lat = lbm.Lattice(p["nx"], p["ny"], steps, p["density"], p["accel"], p["omega"], mask, obstacle_lines=lines,
-                      rank=rank, size=size, device=rank)
+                      rank=rank, size=size, device=rank, engine=engine)
     up, down, _ = ring.exchange_blobs(dist, torch, lat.rank_export(), rank, size, device="cpu")
     lat.rank_connect(up, down)
     lat.run(steps // 2)
@@ -384,14 +437,16 @@ def _rank_worker(rank, size, port, grid, steps, out_dir):
     np.save(os.path.join(out_dir, f"cells_{rank}.npy"), f)
     if rank == 0:
         np.save(os.path.join(out_dir, "av.npy"), av)
-    dist.barrier()                  # neighbours must be done with my halo slots before I free them
+    lat.rank_disconnect()           # CUDA IPC: importers unmap, then a barrier, then the exporters free
+    dist.barrier()
     lat.close()
     dist.destroy_process_group()
 
 
 @pytest.mark.timeout(600)
+@pytest.mark.parametrize("engine", [0, 1])
 @pytest.mark.parametrize("size,grid,steps", [(2, "128x256", 200), (4, "1024x1024", 60), (8, "128x128", 100)])
-def test_one_process_per_gpu_equals_single_gpu(lbm, tmp_path, size, grid, steps):
+def test_one_process_per_gpu_equals_single_gpu(lbm, tmp_path, size, grid, steps, engine):
     """lbm_create_rank / lbm_rank_export / lbm_rank_connect (CUDA IPC handles of the halo slots, exchanged by
     the host program - here torch.distributed over gloo): N processes, one slab each, must reproduce the
     single-GPU lattice bit for bit and its av_vels after the one sum over ranks (d2q9-bgk.c:445-446)."""
@@ -406,7 +461,7 @@ def test_one_process_per_gpu_equals_single_gpu(lbm, tmp_path, size, grid, steps)
     with socket.socket() as s:
         s.bind(("127.0.0.1", 0))
         port = s.getsockname()[1]
-    mp.spawn(_rank_worker, args=(size, port, grid, steps, str(tmp_path)), nprocs=size, join=True)
+    mp.spawn(_rank_worker, args=(size, port, grid, steps, str(tmp_path), engine), nprocs=size, join=True)
     fn = np.concatenate([np.load(tmp_path / f"cells_{r}.npy") for r in range(size)], axis=1)
     assert np.array_equal(f1, fn)
     np.testing.assert_allclose(np.load(tmp_path / "av.npy"), av1, rtol=3e-7)

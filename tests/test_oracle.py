@@ -10,7 +10,7 @@ import os
 import numpy as np
 import pytest
 
-from helpers import check_py_max_pcnt, load_grid, random_case
+from helpers import assert_final_state_matches_ref_hash, check_py_max_pcnt, load_grid, load_ref_hash, random_case
 
 
 def run_oracle(oracle, grid, steps):
@@ -36,6 +36,19 @@ def test_oracle_large_grid_prefix_matches_reference(oracle, golden):
     g = golden("ref_short_1024x1024_200")
     p, mask, f, av = run_oracle(oracle, "1024x1024", 40)
     assert np.array_equal(av, g["av_vels"][:40])
+
+
+@pytest.mark.parametrize("grid,steps", [("128x256", 200), ("4096x1024", 20), ("8192x1024", 20), ("16384x1024", 20)])
+def test_oracle_matches_reference_hashes_on_the_large_baseline_configs(oracle, grid, steps):
+    """BASELINE.json's row-decomposed / strong-scaling configurations (the bench headline 16384x1024 among them):
+    the oracle's four final-state planes hash to what the UNMODIFIED reference wrote after `steps` timesteps
+    (tests/golden/ref_hash_*.json), av_vels equal bit for bit - so the oracle is pinned at the sizes the
+    -m gpu tests use it at."""
+    g = load_ref_hash(grid, steps)
+    p, mask, f, av = run_oracle(oracle, grid, steps)
+    assert_final_state_matches_ref_hash(g, *oracle.final_state(f, p["density"], mask))
+    assert np.array_equal(av, g["av_vels"])
+    assert int(mask.sum()) == g["blocked_cells"]
 
 
 def test_oracle_full_run_passes_reference_checker_rule(oracle, golden):

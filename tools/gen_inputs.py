@@ -37,8 +37,9 @@ def vrun(x, ny):
 
 
 def obstacle_cells(grid):
-    """Ordered list of (x, y) lines of obstacles_<grid>.dat."""
-    nx, ny = PARAMS[grid][:2]
+    """Ordered list of (x, y) lines of obstacles_<grid>.dat.  Grids the reference does not ship (e.g. its MPI
+    report's long-x / short-y case 131072x128, report_mpi/report.tex:837-859) follow the wide-grid rule."""
+    nx, ny = PARAMS[grid][:2] if grid in PARAMS else (int(v) for v in grid.split("x"))
     if grid == "128x256":          # open (periodic) top/bottom, a wall across y=127, side walls
         return hrun(127, nx) + vrun(0, ny) + vrun(nx - 1, ny)
     if nx <= 1024:                 # closed box: bottom, top, left, right
@@ -49,6 +50,12 @@ def obstacle_cells(grid):
     # wide grids: bottom, top, right, left, then walls at nx/4 and nx/2
     return (hrun(0, nx) + hrun(ny - 1, nx) + vrun(nx - 1, ny) + vrun(0, ny)
             + vrun(nx // 4, ny) + vrun((nx // 4) * 2, ny))
+
+
+def synthetic_params(grid):
+    """Params of a grid outside the shipped set: the shipped wide grids' values."""
+    nx, ny = (int(v) for v in grid.split("x"))
+    return dict(nx=nx, ny=ny, max_iters=20000, reynolds_dim=10, density=0.1, accel=0.01, omega=1.85)
 
 
 def params_text(grid):
