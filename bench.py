@@ -412,7 +412,9 @@ def parity_case(lbm, torch, dist, grid, steps, rank, world):
         ref_av = np.array([float(v) for v in g["av_vels"]], np.float32)
         res["final_state_sha256_equals_reference"] = bool(same)
         res["av_vels_vs_reference_max_rel_diff"] = float(np.max(np.abs(av - ref_av) / np.abs(ref_av)))
-        ok = ok and same and res["av_vels_vs_reference_max_rel_diff"] <= 1e-4
+        # the reference sums |u| sequentially in fp32 over up to 16.8 M cells (d2q9-bgk.c:335): its own rounding error
+        # reaches 5e-4 there (tests/test_gpu_parity.py holds the device's double-precision sum to 3e-7 of the exact sum)
+        ok = ok and same and res["av_vels_vs_reference_max_rel_diff"] <= 1e-3
     if world > 1:
         t = torch.tensor([int(ok)], device="cuda", dtype=torch.int64)
         dist.all_reduce(t, op=dist.ReduceOp.MIN)

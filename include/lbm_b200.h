@@ -179,13 +179,13 @@ int lbm_host_selftest(int nx, int ny, int size, long long seed);
 int lbm_selftest_math(long long n, long long seed, long long* mismatches);
 
 /* Device stress test of the tagged 16-byte records that carry the halos between GPUs (and the whole lattice
- * of engines 3 and 4): a kernel on `writer_device` rewrites 16 K records living on `reader_device` with
- * {t,t,t,t}, t = 1..rounds, through the product's store (one scalar st.relaxed.sys.b128) while a kernel on
- * `reader_device` keeps reading them through the product's read path (mode 0: ld.relaxed.sys.b128; mode 1: the
+ * of engines 3 and 4): a kernel on `writer_device` keeps rewriting 16 K records living on `reader_device`
+ * with {t,t,t,t}, t = 1, 2, ... through the product's store (one scalar st.relaxed.sys.b128) while a kernel on
+ * `reader_device` reads them `sweeps` x 4 times each through the product's read path (mode 0: ld.relaxed.sys.b128; mode 1: the
  * 16-byte cp.async into shared memory used by the halo staging).  *torn = records seen with mixed words (must be
  * 0), *changes = times a record changed between two consecutive looks (> 0 proves the kernels overlapped).
  * writer_device == reader_device runs both kernels side by side on one GPU. */
-int lbm_selftest_records(int writer_device, int reader_device, int rounds, int mode, long long* torn, long long* changes);
+int lbm_selftest_records(int writer_device, int reader_device, int sweeps, int mode, long long* torn, long long* changes);
 
 /* ---- one process per GPU (torchrun-style launch) -------------------------------
  * Rank r of `size` owns slab r on CUDA device `device`.  After creation every rank

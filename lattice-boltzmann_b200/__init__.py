@@ -120,12 +120,12 @@ def selftest_math(n=1 << 26, seed=1):
     return bad.value
 
 
-def selftest_records(writer_device=0, reader_device=0, rounds=2000, mode=0):
+def selftest_records(writer_device=0, reader_device=0, sweeps=2000, mode=0):
     """(torn, changes): torn 16-byte records seen (must be 0) and value changes observed between consecutive
     looks (> 0: reads and writes overlapped) while one kernel rewrites tagged records and another reads them."""
     lib = load_library()
     torn, changes = ctypes.c_longlong(-1), ctypes.c_longlong(-1)
-    if lib.lbm_selftest_records(writer_device, reader_device, rounds, mode, ctypes.byref(torn), ctypes.byref(changes)):
+    if lib.lbm_selftest_records(writer_device, reader_device, sweeps, mode, ctypes.byref(torn), ctypes.byref(changes)):
         raise LbmError(_err(lib))
     return torn.value, changes.value
 

@@ -232,17 +232,23 @@ __global__ void k_selftest_math(unsigned long long n, unsigned long long seed, i
 
 
 // ---- torn-record stress test (lbm_selftest_records) ---------------------------------------------------
-// Writer: every thread rewrites its records with {t,t,t,t} for t = 1..rounds through st_record, the product's
-// store, at full rate.  Reader (other GPU over NVLink, or other SMs of the same GPU): sweeps the same records
+// Writer: every thread rewrites its records with {t,t,t,t}, t = 1, 2, ... through st_record, the product's
+// store, at full rate, until the host tells it (through a mapped flag) that the reader has finished.  Reader (other GPU over NVLink, or other SMs of the same GPU): sweeps the same records
 // through the product's two read paths - ld_record (mode 0) and the cp.async 16-byte copy into shared memory used
 // by the halo staging (mode 1) - and counts records whose four words are not all equal (TORN) and how many
-// times a record's value changed between two looks (proof that reads and writes really overlapped).  Neither
-// kernel waits for the other, so nothing can hang.
-__global__ void k_records_writer(uint4* slots, int n, unsigned rounds)
+// times a record's value changed between two looks (proof that reads and writes really overlapped).  The reader
+// never waits for the writer and the writer stops on its own after ~10 s, so nothing can hang.
+__global__ void k_records_writer(uint4* slots, int n, volatile int* stop /* host-mapped */, unsigned long long* rounds_done)
 {
-    for (unsigned t = 1; t <= rounds; ++t)
+    const long long t0 = clock64();
+    unsigned t = 1;
+    for (;; ++t) {
         for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
             lbm::st_record(slots + i, __uint_as_float(t), __uint_as_float(t), __uint_as_float(t), t);
+        // until the host says the reader is done; never longer than ~10 s on its own
+        if ((t & 255u) == 0u && (*stop || clock64() - t0 > lbm::kSpinLimitCycles)) break;
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) *rounds_done = t;
 }
 
 __global__ void k_records_reader(const uint4* slots, int n, int sweeps, int mode, unsigned long long* out /* torn, changes */)
@@ -520,7 +526,10 @@ int configure_engine(lbm_ctx* c, int device)
     if (c->engine == 4 && !fits4)
         return fail("engine 4 (one cell per lane) needs nx %% 32 == 0, slabs of at most %lld 32-cell tasks (the largest here "
                     "has %lld) and at most 2 GiB of per-step partial sums", warps4, ntasks);
-    if (c->engine == 0) c->engine = fits4 ? 4 : fits3 ? 3 : 1;
+    // auto never takes engine 4: measured (profiles/r02_small_lattice.md) it ties engine 3 on 128x128 (1.50 vs 1.52 us
+    // per step) and loses from 256x256 on (1.77 vs 1.65; 512x256: 4.72 vs 2.13) - a step is bounded by the L2 hop
+    // between SMs (530-1300 cycles one way), not by the instructions of one warp
+    if (c->engine == 0) c->engine = fits3 ? 3 : 1;
     c->threads = c->opt.threads_per_cta ? c->opt.threads_per_cta : env_int("LBM_THREADS", 256);
     if (c->threads % 32 || c->threads < 32 || c->threads > 512) return fail("threads_per_cta must be a multiple of 32 in [32,512]");
     int per_sm = c->opt.ctas_per_sm ? c->opt.ctas_per_sm : env_int("LBM_CTAS_PER_SM", 2);
@@ -768,21 +777,24 @@ int lbm_selftest_math(long long n, long long seed, long long* mismatches)
     return 0;
 }
 
-int lbm_selftest_records(int writer_device, int reader_device, int rounds, int mode, long long* torn, long long* changes)
+int lbm_selftest_records(int writer_device, int reader_device, int sweeps, int mode, long long* torn, long long* changes)
 {
-    if (!torn || !changes || rounds < 1 || mode < 0 || mode > 1) return fail("bad arguments");
+    if (!torn || !changes || sweeps < 1 || mode < 0 || mode > 1) return fail("bad arguments");
     const int ndev = lbm_device_count();
     if (writer_device < 0 || reader_device < 0 || writer_device >= ndev || reader_device >= ndev)
         return fail("lbm_selftest_records: devices %d / %d but %d visible", writer_device, reader_device, ndev);
     const int n = 64 * 256;                              // 256 KB of records, the size of a 16384-wide slab's inbound slots
     uint4* slots = nullptr;
     unsigned long long* out = nullptr;
+    int* stop = nullptr;
     cudaStream_t sw = nullptr, sr = nullptr;
     CK(cudaSetDevice(reader_device));                    // the slots live with the reader, as the halo slots do
     CK(cudaMalloc(&slots, sizeof(uint4) * n));
     CK(cudaMemset(slots, 0, sizeof(uint4) * n));
-    CK(cudaMalloc(&out, 2 * sizeof(unsigned long long)));
-    CK(cudaMemset(out, 0, 2 * sizeof(unsigned long long)));
+    CK(cudaMalloc(&out, 3 * sizeof(unsigned long long)));
+    CK(cudaMemset(out, 0, 3 * sizeof(unsigned long long)));
+    CK(cudaHostAlloc(&stop, sizeof(int), cudaHostAllocPortable | cudaHostAllocMapped));
+    *stop = 0;
     CK(cudaStreamCreateWithFlags(&sr, cudaStreamNonBlocking));
     CK(cudaDeviceSynchronize());
     if (writer_device != reader_device) {
@@ -796,20 +808,33 @@ int lbm_selftest_records(int writer_device, int reader_device, int rounds, int m
     }
     CK(cudaSetDevice(writer_device));
     CK(cudaStreamCreateWithFlags(&sw, cudaStreamNonBlocking));
+    // Both kernels run once on nothing first: with lazy module loading the FIRST launch of a kernel may have to wait
+    // for the device to go idle, which would serialise reader and writer instead of overlapping them.
+    *stop = 1;
+    k_records_writer<<<1, 32, 0, sw>>>(slots, 0, stop, out + 2);
+    CK(cudaStreamSynchronize(sw));
+    CK(cudaSetDevice(reader_device));
+    k_records_reader<<<1, 32, 0, sr>>>(slots, 0, 0, mode, out);
+    CK(cudaStreamSynchronize(sr));
+    *stop = 0;
+    CK(cudaSetDevice(writer_device));
     // 64 CTAs each: on one GPU both kernels fit side by side (148 SMs), so they overlap there as well
-    k_records_writer<<<64, 256, 0, sw>>>(slots, n, (unsigned)rounds);
+    k_records_writer<<<64, 256, 0, sw>>>(slots, n, stop, out + 2);
     CK(cudaGetLastError());
     CK(cudaSetDevice(reader_device));
-    k_records_reader<<<64, 256, 0, sr>>>(slots, n, std::max(1, rounds / 4), mode, out);
+    k_records_reader<<<64, 256, 0, sr>>>(slots, n, sweeps, mode, out);
     CK(cudaGetLastError());
-    CK(cudaStreamSynchronize(sr));
+    const cudaError_t er = cudaStreamSynchronize(sr);
+    *(volatile int*)stop = 1;                            // the writer ends within 256 rounds of seeing this
+    CK(er);
     CK(cudaSetDevice(writer_device));
     CK(cudaStreamSynchronize(sw));
-    unsigned long long h[2] = {0, 0};
+    unsigned long long h[3] = {0, 0, 0};
     CK(cudaSetDevice(reader_device));
     CK(cudaMemcpy(h, out, sizeof(h), cudaMemcpyDeviceToHost));
     CK(cudaFree(slots));
     CK(cudaFree(out));
+    CK(cudaFreeHost(stop));
     CK(cudaStreamDestroy(sr));
     CK(cudaSetDevice(writer_device));
     CK(cudaStreamDestroy(sw));

@@ -36,6 +36,8 @@ def load(omp=False):
     lib.oracle_run_ranks.argtypes = [_c_int, _c_int, _c_int, _c_float, _c_float, _c_float,
                                      _i32p, _f32p, _f32p, _c_int, _c_int]
     lib.oracle_run_ranks.restype = _c_int
+    lib.oracle_set_exact_sums.argtypes = [ctypes.c_void_p]
+    lib.oracle_set_exact_sums.restype = None
     lib.oracle_run.argtypes = [_c_int, _c_int, _c_int, _c_float, _c_float, _c_float,
                                _i32p, _f32p, _f32p, _c_int]
     lib.oracle_run.restype = _c_int
@@ -67,16 +69,22 @@ class Oracle:
         self.lib.oracle_init(nx, ny, density, f)
         return f
 
-    def run(self, nx, ny, iters, density, accel, omega, obst, f=None, ranks=1):
-        """Returns (lattice, tot_u[iters] un-normalised)."""
+    def run(self, nx, ny, iters, density, accel, omega, obst, f=None, ranks=1, exact=False):
+        """Returns (lattice, tot_u[iters] un-normalised); with exact=True additionally the per-step sums of the
+        same per-cell fp32 speeds accumulated in double (float64[iters])."""
         from_state = f is not None
         f = np.ascontiguousarray(f, np.float32).copy() if from_state else np.empty((9, ny, nx), np.float32)
         tot_u = np.zeros(max(iters, 1), np.float32)
-        rc = self.lib.oracle_run_ranks(nx, ny, iters, density, accel, omega,
-                                       np.ascontiguousarray(obst, np.int32), f, tot_u, ranks, int(from_state))
+        sums = np.zeros(max(iters, 1), np.float64)
+        self.lib.oracle_set_exact_sums(sums.ctypes.data if exact else None)
+        try:
+            rc = self.lib.oracle_run_ranks(nx, ny, iters, density, accel, omega,
+                                           np.ascontiguousarray(obst, np.int32), f, tot_u, ranks, int(from_state))
+        finally:
+            self.lib.oracle_set_exact_sums(None)
         if rc != 0:
             raise RuntimeError("oracle_run_ranks failed")
-        return f, tot_u[:iters]
+        return (f, tot_u[:iters], sums[:iters]) if exact else (f, tot_u[:iters])
 
     def accelerate_flow(self, f, density, accel, obst):
         _, ny, nx = f.shape

@@ -100,12 +100,16 @@ def test_large_baseline_configs_match_oracle_and_reference_bit_exact(lbm, oracle
     """BASELINE.json configs 4 and 5 at FULL size - 4096x1024, 8192x1024 and the bench headline 16384x1024
     (reference: timestep, d2q9-bgk.c:268-339 on input_16384x1024.params) - on one GPU:
       * all nine populations of every cell equal the oracle's bit for bit (the OpenMP oracle needs
-        about a second for 20 steps of 16.8 M cells), av_vels within AV_RTOL of its sequential fp32 sum;
+        about a second for 20 steps of 16.8 M cells);
+      * av_vels: the device sums the bit-identical per-cell |u| in double, so it must agree to fp32 rounding
+        (3e-7) with the oracle's double-precision sum of the same values; against the reference's own
+        SEQUENTIAL fp32 sum over up to 16.8 M cells (:335) only to that sum's rounding error, 1e-3 (measured:
+        1.2e-4 at 4 M cells, 4.9e-4 at 16.8 M);
       * the four final-state planes hash to what the UNMODIFIED reference (oracle/_ref/ref-serial) wrote
         for the same input (tests/golden/ref_hash_*.json, made by tests/golden/make_golden.py)."""
     g = load_ref_hash(grid, steps)
     p, mask, lines = load_grid(grid)
-    ref_f, ref_tot = oracle.run(p["nx"], p["ny"], steps, p["density"], p["accel"], p["omega"], mask)
+    ref_f, ref_tot, ref_exact = oracle.run(p["nx"], p["ny"], steps, p["density"], p["accel"], p["omega"], mask, exact=True)
     with make(lbm, p, mask, lines, iters=steps) as lat:
         lat.run(steps)
         f = lat.cells()
@@ -114,8 +118,9 @@ def test_large_baseline_configs_match_oracle_and_reference_bit_exact(lbm, oracle
         inv = lat.inv_free_cells()
     assert np.array_equal(f.view(np.uint32), ref_f.view(np.uint32)), "lattice differs from the oracle"
     assert_final_state_matches_ref_hash(g, *fs)
-    np.testing.assert_allclose(av, ref_tot * inv, rtol=AV_RTOL)
-    np.testing.assert_allclose(av, g["av_vels"], rtol=AV_RTOL)
+    np.testing.assert_allclose(av, (ref_exact.astype(np.float32) * inv).astype(np.float32), rtol=3e-7)
+    np.testing.assert_allclose(av, ref_tot * inv, rtol=1e-3)
+    np.testing.assert_allclose(av, g["av_vels"], rtol=1e-3)
 
 
 @pytest.mark.parametrize("grid", ["128x128", "128x256", "256x256", "1024x1024"])
@@ -322,7 +327,7 @@ def test_tagged_records_are_never_torn_one_gpu(lbm, mode):
     written and read as ONE unit (st/ld.relaxed.sys.b128; mode 1: the 16-byte cp.async of the halo staging).
     A writer kernel rewrites 16 K records at full rate while a reader kernel on other SMs keeps looking: no
     record may ever show mixed words, and the reader must really have seen values change under it."""
-    torn, changes = lbm.selftest_records(0, 0, rounds=20000, mode=mode)
+    torn, changes = lbm.selftest_records(0, 0, sweeps=3000, mode=mode)
     assert torn == 0
     assert changes > 1000, "reader and writer did not overlap; the test proved nothing"
 
@@ -337,7 +342,7 @@ def test_tagged_records_are_never_torn_over_nvlink(lbm, mode):
     if _ngpu(lbm) < 2:
         pytest.skip("needs 2 GPUs")
     for w, r in ((1, 0), (0, 1)):
-        torn, changes = lbm.selftest_records(w, r, rounds=20000, mode=mode)
+        torn, changes = lbm.selftest_records(w, r, sweeps=3000, mode=mode)
         assert torn == 0
         assert changes > 1000, "reader and writer did not overlap; the test proved nothing"
 
