@@ -21,6 +21,12 @@ all: $(EXE)
 $(LIB): $(PKG)/csrc/lbm_api.cu $(PKG)/csrc/lbm_plan.cpp $(PKG)/csrc/lbm_kernels.cuh $(PKG)/csrc/lbm_device.cuh $(PKG)/csrc/lbm_plan.hpp include/lbm_b200.h
 	$(NVCC) $(NVFLAGS) -shared $(PKG)/csrc/lbm_api.cu $(PKG)/csrc/lbm_plan.cpp -o $@
 
+# the self-checking build (stand-in for compute-sanitizer, see lbm_device.cuh): LBM_LIBRARY=$(LIB_CHECKED) pytest -m gpu
+LIB_CHECKED = $(PKG)/liblbm_b200_checked.so
+checked: $(LIB_CHECKED)
+$(LIB_CHECKED): $(PKG)/csrc/lbm_api.cu $(PKG)/csrc/lbm_plan.cpp $(PKG)/csrc/lbm_kernels.cuh $(PKG)/csrc/lbm_device.cuh $(PKG)/csrc/lbm_plan.hpp include/lbm_b200.h
+	$(NVCC) $(NVFLAGS) -DLBM_CHECKED -shared $(PKG)/csrc/lbm_api.cu $(PKG)/csrc/lbm_plan.cpp -o $@
+
 $(EXE): src/d2q9-bgk.c src/fmt_e12.h include/lbm_b200.h $(LIB)
 	$(CC) $(CFLAGS) src/d2q9-bgk.c -L$(PKG) -llbm_b200 -Wl,-rpath,'$$ORIGIN/$(PKG)' -lm -o $@
 
@@ -34,11 +40,11 @@ $(REF_FINAL_STATE_FILE) $(REF_AV_VELS_FILE):
 check: $(REF_FINAL_STATE_FILE) $(REF_AV_VELS_FILE)
 	python $(CHECKER) --ref-av-vels-file=$(REF_AV_VELS_FILE) --ref-final-state-file=$(REF_FINAL_STATE_FILE) --av-vels-file=$(AV_VELS_FILE) --final-state-file=$(FINAL_STATE_FILE)
 
-# compute-sanitizer over the small grids, every engine (GPU box): see tools/sanitize.sh
-sanitize: all
-	bash tools/sanitize.sh
+# the parity suite against the self-checking build (GPU box); compute-sanitizer itself is closed on this pool
+sanitize: all checked
+	LBM_LIBRARY=$(CURDIR)/$(LIB_CHECKED) python -m pytest tests -m gpu -q -k "oracle or slabs or engines or checked"
 
-.PHONY: all check clean oracle sanitize
+.PHONY: all check clean oracle sanitize checked
 
 clean:
-	rm -f $(EXE) $(LIB)
+	rm -f $(EXE) $(LIB) $(LIB_CHECKED)

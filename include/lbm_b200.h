@@ -82,6 +82,11 @@ int lbm_create(lbm_ctx** out, const lbm_params* params, const int* obstacles, in
  * work first, so it is safe straight after lbm_run.  One-process-per-GPU mode: see lbm_rank_disconnect. */
 void lbm_destroy(lbm_ctx* ctx);
 
+/* Device buffers of destroyed contexts are kept per process (by device and exact size, up to LBM_CACHE_MB
+ * megabytes, default 3072, 0 = off) for the next lbm_create of the same shape: cudaMalloc / cudaFree of lattice-sized
+ * buffers cost tens of milliseconds, more than a short run.  lbm_trim_cache returns them to the driver. */
+int lbm_trim_cache(void);
+
 /* ---- the hot path ------------------------------------------------------------ */
 
 /* Replaces `iters` trips of the time loop body (d2q9-bgk.c:191-197):
@@ -134,6 +139,11 @@ int lbm_total_density(lbm_ctx* ctx, float* out);
 /* ---- introspection ------------------------------------------------------------ */
 
 int lbm_abi_version(void);
+/* 1 if this library was built with -DLBM_CHECKED (`make checked`): every lattice / record / halo-slot access of the
+ * timestep kernels is range- and alignment-checked against the allocations registered for the device, buffers start
+ * poisoned with NaN bytes, and lbm_sync fails on a violation.  The stand-in for compute-sanitizer's memcheck and
+ * initcheck, which this GPU pool does not allow.  Select it with LBM_LIBRARY=<path> in the Python mirror. */
+int lbm_checked_build(void);
 const char* lbm_last_error(void);
 /* number of usable CUDA devices (0 if none / no driver). */
 int lbm_device_count(void);

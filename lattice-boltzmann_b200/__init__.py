@@ -47,6 +47,7 @@ _IP = ctypes.POINTER(ctypes.c_int)
 SYMBOLS = {
     "lbm_create": (ctypes.c_int, [ctypes.POINTER(_P), ctypes.POINTER(Params), _P, ctypes.c_int, ctypes.POINTER(Options)]),
     "lbm_destroy": (None, [_P]),
+    "lbm_trim_cache": (ctypes.c_int, []),
     "lbm_run": (ctypes.c_int, [_P, ctypes.c_int]),
     "lbm_sync": (ctypes.c_int, [_P]),
     "lbm_get_av_vels": (ctypes.c_int, [_P, _P, ctypes.c_int]),
@@ -57,6 +58,7 @@ SYMBOLS = {
     "lbm_av_velocity": (ctypes.c_int, [_P, _FP]),
     "lbm_total_density": (ctypes.c_int, [_P, _FP]),
     "lbm_abi_version": (ctypes.c_int, []),
+    "lbm_checked_build": (ctypes.c_int, []),
     "lbm_last_error": (ctypes.c_char_p, []),
     "lbm_device_count": (ctypes.c_int, []),
     "lbm_steps_done": (ctypes.c_int, [_P]),
@@ -86,7 +88,7 @@ def load_library(path=None):
     global _lib
     if _lib is not None and path is None:
         return _lib
-    path = path or LIB_PATH
+    path = path or os.environ.get("LBM_LIBRARY") or LIB_PATH      # LBM_LIBRARY: e.g. the self-checking build (`make checked`)
     if not os.path.exists(path):
         raise LbmError(f"{path} not found: build it with `make` (nvcc, sm_100a); there is no fallback")
     lib = ctypes.CDLL(path)
@@ -128,6 +130,11 @@ def selftest_records(writer_device=0, reader_device=0, sweeps=2000, mode=0):
     if lib.lbm_selftest_records(writer_device, reader_device, sweeps, mode, ctypes.byref(torn), ctypes.byref(changes)):
         raise LbmError(_err(lib))
     return torn.value, changes.value
+
+
+def trim_cache():
+    """Returns the device buffers cached from destroyed lattices to the driver."""
+    load_library().lbm_trim_cache()
 
 
 def device_count():

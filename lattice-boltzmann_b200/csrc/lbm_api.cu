@@ -14,6 +14,7 @@
 #include <stdexcept>
 #include <string>
 #include <thread>
+#include <unordered_map>
 #include <vector>
 
 #include "../../include/lbm_b200.h"
@@ -39,6 +40,157 @@ int fail(const char* fmt, ...)
         if (e_ != cudaSuccess)                                                                     \
             return fail("%s failed at %s:%d: %s", #call, __FILE__, __LINE__, cudaGetErrorString(e_)); \
     } while (0)
+
+// ---- device buffer cache --------------------------------------------------------------------------------
+// cudaMalloc / cudaFree of the lattice buffers cost 10-100 ms per context on the B200 boxes (cudaFree of a 600 MB
+// buffer has been seen to stall for up to a second: it synchronises the device and unmaps), which a caller that
+// creates a context per job pays on its critical path (bench.py e2e: 1024x1024 ran 211 ms and spent 73 ms in
+// destroy).  Freed buffers are therefore kept per process, keyed by (device, exact size), up to LBM_CACHE_MB
+// (default 3072; 0 disables the cache) and handed to the next lbm_create that asks for the same size; beyond the
+// limit the oldest entries are really freed.  lbm_trim_cache() empties it.  Contents are never trusted: every
+// buffer whose initial value matters is (re)initialised by slab_create as before.
+struct DevCache {
+    struct Entry { int dev; size_t bytes; void* p; };
+    std::mutex mu;
+    std::vector<Entry> idle;                                          // oldest first
+    std::unordered_map<void*, std::pair<int, size_t>> live;           // handed out, not yet returned
+    size_t idle_bytes = 0;
+    static size_t limit()
+    {
+        const char* e = getenv("LBM_CACHE_MB");
+        return (size_t)((e && *e) ? std::max(0, atoi(e)) : 3072) << 20;
+    }
+};
+DevCache g_cache;
+
+cudaError_t dmalloc_bytes(void** out, size_t bytes)
+{
+    int dev = 0;
+    cudaGetDevice(&dev);
+    bytes = std::max<size_t>(bytes, 1);
+    {
+        std::lock_guard<std::mutex> g(g_cache.mu);
+        for (size_t i = g_cache.idle.size(); i-- > 0;) {              // newest first: most likely still mapped hot
+            if (g_cache.idle[i].dev == dev && g_cache.idle[i].bytes == bytes) {
+                *out = g_cache.idle[i].p;
+                g_cache.idle_bytes -= bytes;
+                g_cache.idle.erase(g_cache.idle.begin() + (long)i);
+                g_cache.live[*out] = {dev, bytes};
+                return cudaSuccess;
+            }
+        }
+    }
+    const cudaError_t e = cudaMalloc(out, bytes);
+    if (e == cudaSuccess) {
+        std::lock_guard<std::mutex> g(g_cache.mu);
+        g_cache.live[*out] = {dev, bytes};
+    }
+    return e;
+}
+
+// In the checked build every buffer handed out (fresh or recycled) starts as 0xFF bytes = NaN, so a read of
+// never-written memory shows up in the bit-exact parity tests.
+template <class T> cudaError_t dmalloc(T** out, size_t bytes)
+{
+    cudaError_t e = dmalloc_bytes((void**)out, bytes);
+#ifdef LBM_CHECKED
+    if (e == cudaSuccess) e = cudaMemset(*out, 0xFF, std::max<size_t>(bytes, 1));
+    if (e == cudaSuccess) e = cudaDeviceSynchronize();
+#endif
+    return e;
+}
+
+// Returns a buffer to the cache (or frees it when the cache is off / full).  The caller has synchronised its streams.
+void dfree(void* p)
+{
+    if (!p) return;
+    std::vector<DevCache::Entry> evict;
+    {
+        std::lock_guard<std::mutex> g(g_cache.mu);
+        auto it = g_cache.live.find(p);
+        if (it == g_cache.live.end()) { evict.push_back({-1, 0, p}); }
+        else {
+            const DevCache::Entry e{it->second.first, it->second.second, p};
+            g_cache.live.erase(it);
+            const size_t lim = DevCache::limit();
+            if (e.bytes > lim) evict.push_back(e);
+            else {
+                g_cache.idle.push_back(e);
+                g_cache.idle_bytes += e.bytes;
+                while (g_cache.idle_bytes > lim && !g_cache.idle.empty()) {
+                    evict.push_back(g_cache.idle.front());
+                    g_cache.idle_bytes -= g_cache.idle.front().bytes;
+                    g_cache.idle.erase(g_cache.idle.begin());
+                }
+            }
+        }
+    }
+    if (evict.empty()) return;
+    int cur = 0;
+    cudaGetDevice(&cur);
+    for (const auto& e : evict) {
+        if (e.dev >= 0) cudaSetDevice(e.dev);
+        cudaFree(e.p);
+    }
+    cudaSetDevice(cur);
+}
+
+// ---- checked build: the per-device table of valid address ranges (see lbm_device.cuh) ---------------------
+#ifdef LBM_CHECKED
+struct CheckRange { int dev; unsigned long long lo, hi; const void* owner; };
+std::mutex g_check_mu;
+std::vector<CheckRange> g_check_ranges;
+
+int check_upload(int dev)
+{
+    lbm::CheckTable t;
+    memset(&t, 0, sizeof(t));
+    {
+        std::lock_guard<std::mutex> g(g_check_mu);
+        for (const CheckRange& r : g_check_ranges)
+            if (r.dev == dev && t.n < lbm::kMaxCheckRanges) { t.lo[t.n] = r.lo; t.hi[t.n] = r.hi; ++t.n; }
+    }
+    int cur = 0;
+    cudaGetDevice(&cur);
+    cudaSetDevice(dev);
+    // keep the violation record, replace the ranges
+    lbm::CheckTable old;
+    cudaError_t e = cudaMemcpyFromSymbol(&old, lbm::g_check, sizeof(old));
+    if (e == cudaSuccess) { t.bad_count = old.bad_count; t.bad_ptr = old.bad_ptr; t.bad_bytes = old.bad_bytes; }
+    e = cudaMemcpyToSymbol(lbm::g_check, &t, sizeof(t));
+    cudaSetDevice(cur);
+    return e == cudaSuccess ? 0 : fail("checked build: cudaMemcpyToSymbol: %s", cudaGetErrorString(e));
+}
+void check_add(int dev, const void* owner, const void* p, size_t bytes)
+{
+    if (!p || !bytes) return;
+    std::lock_guard<std::mutex> g(g_check_mu);
+    g_check_ranges.push_back({dev, (unsigned long long)p, (unsigned long long)p + bytes, owner});
+}
+void check_remove(const void* owner)
+{
+    std::lock_guard<std::mutex> g(g_check_mu);
+    g_check_ranges.erase(std::remove_if(g_check_ranges.begin(), g_check_ranges.end(), [&](const CheckRange& r) { return r.owner == owner; }),
+                         g_check_ranges.end());
+}
+// after a synchronisation: did any kernel on `dev` touch memory outside its ranges?
+int check_report(int dev)
+{
+    lbm::CheckTable t;
+    if (cudaMemcpyFromSymbol(&t, lbm::g_check, sizeof(t)) != cudaSuccess) { cudaGetLastError(); return 0; }
+    if (t.bad_count == 0) return 0;
+    const unsigned long long n = t.bad_count, p = t.bad_ptr, b = t.bad_bytes;
+    t.bad_count = t.bad_ptr = t.bad_bytes = 0;
+    cudaMemcpyToSymbol(lbm::g_check, &t, sizeof(t));
+    return fail("checked build: %llu out-of-range or misaligned device accesses on device %d; first: %llu bytes at %p "
+                "(status 3)", n, dev, b, (void*)p);
+}
+#else
+inline int check_upload(int) { return 0; }
+inline void check_add(int, const void*, const void*, size_t) {}
+inline void check_remove(const void*) {}
+inline int check_report(int) { return 0; }
+#endif
 
 struct Slab {
     int device = 0;
@@ -398,9 +550,16 @@ int download(int device, cudaStream_t stream, const std::vector<Piece>& pieces)
     }
     int nt = (int)std::min<size_t>(4, chunks.size() / 4);
     if (const char* e = getenv("LBM_HOST_THREADS")) nt = std::min(nt, std::max(1, atoi(e)));
+    // a destination in page-locked memory (the caller's long-lived result planes) is DMA-ed into directly
+    bool pinned_dst = !pieces.empty();
+    for (const Piece& pc : pieces) {
+        cudaPointerAttributes at;
+        if (cudaPointerGetAttributes(&at, pc.dst) != cudaSuccess) { cudaGetLastError(); pinned_dst = false; break; }
+        if (at.type != cudaMemoryTypeHost) { pinned_dst = false; break; }
+    }
     // below 128 MB the plain copy wins once the one-off pinning of the staging block is counted (8 ranks x 75 MB at
     // 8 GPUs: ~20 ms plain against ~10 ms + a first call of 60-130 ms)
-    if (total < ((size_t)128 << 20) || nt < 1 || env_int("LBM_PLAIN_DOWNLOAD", 0)) {
+    if (pinned_dst || total < ((size_t)128 << 20) || nt < 1 || env_int("LBM_PLAIN_DOWNLOAD", 0)) {
         for (const Piece& pc : pieces) CK(cudaMemcpyAsync(pc.dst, pc.src, pc.bytes, cudaMemcpyDeviceToHost, stream));
         CK(cudaStreamSynchronize(stream));
         return 0;
@@ -453,19 +612,21 @@ void slab_free(Slab& s)
     auto now = [] { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
     const double t0 = now();
     cudaSetDevice(s.device);
+    check_remove(&s);
+    check_upload(s.device);
     if (s.graph) cudaGraphExecDestroy(s.graph);
     if (s.ipc_ll_up) cudaIpcCloseMemHandle(s.ipc_ll_up);
     if (s.ipc_ll_down && s.ipc_ll_down != s.ipc_ll_up) cudaIpcCloseMemHandle(s.ipc_ll_down);
     if (s.ipc_rec_up) cudaIpcCloseMemHandle(s.ipc_rec_up);
     if (s.ipc_rec_down && s.ipc_rec_down != s.ipc_rec_up) cudaIpcCloseMemHandle(s.ipc_rec_down);
     const double t1 = now();
-    cudaFree(s.buf[0]);
+    dfree(s.buf[0]);
     const double t2 = now();
-    cudaFree(s.buf[1]);
+    dfree(s.buf[1]);
     const double t3 = now();
-    cudaFree(s.mask); cudaFree(s.sched); cudaFree(s.flags);
-    cudaFree(s.partials); cudaFree(s.tot); cudaFree(s.status); cudaFree(s.step_ptr); cudaFree(s.fields);
-    cudaFree(s.scal); cudaFree(s.prof); cudaFree(s.ll_in); cudaFree(s.rec);
+    dfree(s.mask); dfree(s.sched); dfree(s.flags);
+    dfree(s.partials); dfree(s.tot); dfree(s.status); dfree(s.step_ptr); dfree(s.fields);
+    dfree(s.scal); dfree(s.prof); dfree(s.ll_in); dfree(s.rec);
     const double t4 = now();
     if (s.ev_start) cudaEventDestroy(s.ev_start);
     if (s.ev_stop) cudaEventDestroy(s.ev_stop);
@@ -479,12 +640,14 @@ void slab_free(Slab& s)
 // Decides engine, CTA shape and the per-slab CTA budget from the device and the options.
 int configure_engine(lbm_ctx* c, int device)
 {
-    cudaDeviceProp prop;
-    CK(cudaGetDeviceProperties(&prop, device));
-    if (prop.major < 10)
-        return fail("device %d (%s, sm_%d%d) is not a Blackwell-class GPU; this library is built for sm_100a only",
-                    device, prop.name, prop.major, prop.minor);
-    const int sms = prop.multiProcessorCount;
+    // attributes, not cudaGetDeviceProperties: that call alone costs 2-3 ms, as much as the rest of lbm_create
+    int cc_major = 0, cc_minor = 0, sms = 0;
+    CK(cudaDeviceGetAttribute(&cc_major, cudaDevAttrComputeCapabilityMajor, device));
+    CK(cudaDeviceGetAttribute(&cc_minor, cudaDevAttrComputeCapabilityMinor, device));
+    CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+    if (cc_major < 10)
+        return fail("device %d (sm_%d%d) is not a Blackwell-class GPU; this library is built for sm_100a only",
+                    device, cc_major, cc_minor);
     c->strict = (c->opt.strict_fp != 2);
     if (env_int("LBM_FAST_FP", 0)) c->strict = false;
     c->engine = c->opt.engine ? c->opt.engine : env_int("LBM_ENGINE", 0);
@@ -554,6 +717,9 @@ int configure_engine(lbm_ctx* c, int device)
 int slab_create(lbm_ctx* c, Slab& s, int rank, int device, const int* obst)
 {
     const lbm_params& P = c->prm;
+    const bool report = env_int("LBM_REPORT", 0) > 1;           // set-up phase times on stderr (host clock)
+    auto now = [] { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+    const double t_begin = now();
     s.device = device;
     CK(cudaSetDevice(device));
     CK(cudaFuncSetAttribute(persistent_fn(c->strict, c->size > 1), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->stage_bytes));
@@ -565,6 +731,7 @@ int slab_create(lbm_ctx* c, Slab& s, int rank, int device, const int* obst)
     } catch (const std::exception& e) {
         return fail("%s", e.what());
     }
+    const double t_plan = now();
     const lbm::SlabPlan& pl = s.plan;
     const long long ps = (long long)(pl.rows + 2) * P.nx;
     if (9 * ps >= (1LL << 32))
@@ -574,28 +741,29 @@ int slab_create(lbm_ctx* c, Slab& s, int rank, int device, const int* obst)
     const int G = (c->engine == 4) ? pl.rows * (P.nx / 32) : pl.num_ctas;
     const int pitch = ((P.nx + 7) / 8 + 15) / 16 * 16;
 
-    for (int i = 0; i < 2; ++i) CK(cudaMalloc(&s.buf[i], sizeof(float) * 9 * ps));
-    CK(cudaMalloc(&s.mask, (size_t)(pl.rows + 2) * pitch));
-    CK(cudaMalloc(&s.flags, sizeof(unsigned) * G));
-    CK(cudaMalloc(&s.partials, sizeof(double) * (size_t)std::max(P.max_iters, 1) * G));
-    CK(cudaMalloc(&s.tot, sizeof(double) * std::max(P.max_iters, 1)));
-    CK(cudaMalloc(&s.status, sizeof(int)));
-    CK(cudaMalloc(&s.step_ptr, sizeof(int)));
-    CK(cudaMalloc(&s.scal, sizeof(double) * 2));
+    for (int i = 0; i < 2; ++i) CK(dmalloc(&s.buf[i], sizeof(float) * 9 * ps));
+    CK(dmalloc(&s.mask, (size_t)(pl.rows + 2) * pitch));
+    CK(dmalloc(&s.flags, sizeof(unsigned) * G));
+    CK(dmalloc(&s.partials, sizeof(double) * (size_t)std::max(P.max_iters, 1) * G));
+    CK(dmalloc(&s.tot, sizeof(double) * std::max(P.max_iters, 1)));
+    CK(dmalloc(&s.status, sizeof(int)));
+    CK(dmalloc(&s.step_ptr, sizeof(int)));
+    CK(dmalloc(&s.scal, sizeof(double) * 2));
     CK(cudaMemsetAsync(s.flags, 0, sizeof(unsigned) * G, s.stream));
     if (c->size > 1) {     // tag 0 = never written; the first run's tags start at 1
-        CK(cudaMalloc(&s.ll_in, sizeof(uint4) * 4 * (size_t)P.nx));
+        CK(dmalloc(&s.ll_in, sizeof(uint4) * 4 * (size_t)P.nx));
         CK(cudaMemsetAsync(s.ll_in, 0, sizeof(uint4) * 4 * (size_t)P.nx, s.stream));
     }
     if (c->engine == 3 || c->engine == 4) {  // tag 0 = never written
         const size_t bytes = sizeof(uint4) * 2 * 3 * (size_t)(pl.rows + 2) * P.nx;
-        CK(cudaMalloc(&s.rec, bytes));
+        CK(dmalloc(&s.rec, bytes));
         CK(cudaMemsetAsync(s.rec, 0, bytes, s.stream));
     }
     CK(cudaMemsetAsync(s.tot, 0, sizeof(double) * std::max(P.max_iters, 1), s.stream));
     CK(cudaMemsetAsync(s.status, 0, sizeof(int), s.stream));
     CK(cudaMemsetAsync(s.step_ptr, 0, sizeof(int), s.stream));
 
+    const double t_alloc = now();
     // schedule arrays, one allocation: task_order as (row, chunk) pairs first (8-byte aligned), then
     // task_begin | n_interior | n_edge | dep_begin | deps
     std::vector<int> h;
@@ -607,11 +775,13 @@ int slab_create(lbm_ctx* c, Slab& s, int rank, int device, const int* obst)
     const size_t o_tb = put(pl.task_begin), o_ni = put(pl.n_interior), o_ne = put(pl.n_edge),
                  o_db = put(pl.dep_begin), o_dp = put(pl.deps);
     h.push_back(0);
-    CK(cudaMalloc(&s.sched, sizeof(int) * h.size()));
+    CK(dmalloc(&s.sched, sizeof(int) * h.size()));
     CK(cudaMemcpyAsync(s.sched, h.data(), sizeof(int) * h.size(), cudaMemcpyHostToDevice, s.stream));
     c->h2d_bytes += (long long)(sizeof(int) * h.size());
 
+    const double t_sched = now();
     const std::vector<unsigned char> m = pack_mask(obst, P.nx, P.ny, pl.row_start, pl.rows, pitch);
+    const double t_pack = now();
     CK(cudaMemcpyAsync(s.mask, m.data(), m.size(), cudaMemcpyHostToDevice, s.stream));
     c->h2d_bytes += (long long)m.size();
 
@@ -621,6 +791,9 @@ int slab_create(lbm_ctx* c, Slab& s, int rank, int device, const int* obst)
     k_fill_uniform<<<(unsigned)((ps + 255) / 256), 256, 0, s.stream>>>(s.buf[1], ps, w0, w1, w2);
     CK(cudaGetLastError());
     CK(cudaStreamSynchronize(s.stream));   // h and m go out of scope
+    if (report)
+        fprintf(stderr, "slab_create[%d]: stream/events+plan %.4f, allocation %.4f, schedule upload %.4f, mask pack %.4f, "
+                "uploads+fill+sync %.4f s\n", rank, t_plan - t_begin, t_alloc - t_plan, t_sched - t_alloc, t_pack - t_sched, now() - t_pack);
 
     SlabDev& d = s.dev;
     d.buf[0] = s.buf[0]; d.buf[1] = s.buf[1];
@@ -640,11 +813,21 @@ int slab_create(lbm_ctx* c, Slab& s, int rank, int device, const int* obst)
     d.prof = nullptr;
     if (env_int("LBM_PROFILE", 0)) {
         const size_t n = sizeof(long long) * (size_t)G * lbm::kMaxWarps * 4;
-        CK(cudaMalloc(&s.prof, n));
+        CK(dmalloc(&s.prof, n));
         CK(cudaMemset(s.prof, 0, n));
         d.prof = s.prof;
     }
-    return 0;
+    // checked build: what this slab's kernels may touch on this device (LBM_CHECK_INJECT=1 registers lattice B one
+    // row short, so that the checker itself can be tested: legitimate accesses to its last row must then be caught)
+    const size_t inject = env_int("LBM_CHECK_INJECT", 0) ? sizeof(float) * (size_t)P.nx : 0;
+    check_add(device, &s, s.buf[0], sizeof(float) * 9 * ps);
+    check_add(device, &s, s.buf[1], sizeof(float) * 9 * ps - inject);
+    check_add(device, &s, s.mask, (size_t)(pl.rows + 2) * pitch);
+    check_add(device, &s, s.flags, sizeof(unsigned) * G);
+    check_add(device, &s, s.partials, sizeof(double) * (size_t)std::max(P.max_iters, 1) * G);
+    check_add(device, &s, s.ll_in, sizeof(uint4) * 4 * (size_t)P.nx);
+    check_add(device, &s, s.rec, sizeof(uint4) * 2 * 3 * (size_t)(pl.rows + 2) * P.nx);
+    return check_upload(device);
 }
 
 int count_cells(lbm_ctx* c, const int* obst)
@@ -693,6 +876,14 @@ void describe(lbm_ctx* c)
 extern "C" {
 
 int lbm_abi_version(void) { return LBM_ABI_VERSION; }
+int lbm_checked_build(void)
+{
+#ifdef LBM_CHECKED
+    return 1;
+#else
+    return 0;
+#endif
+}
 const char* lbm_last_error(void) { return g_err; }
 
 int lbm_device_count(void)
@@ -843,6 +1034,22 @@ int lbm_selftest_records(int writer_device, int reader_device, int sweeps, int m
     return 0;
 }
 
+int lbm_trim_cache(void)
+{
+    std::vector<DevCache::Entry> all;
+    {
+        std::lock_guard<std::mutex> g(g_cache.mu);
+        all.swap(g_cache.idle);
+        g_cache.idle_bytes = 0;
+    }
+    int cur = 0;
+    cudaGetDevice(&cur);
+    for (const auto& e : all) { cudaSetDevice(e.dev); cudaFree(e.p); }
+    cudaSetDevice(cur);
+    cudaGetLastError();
+    return 0;
+}
+
 void lbm_destroy(lbm_ctx* c)
 {
     if (!c) return;
@@ -868,7 +1075,10 @@ static int create_common(lbm_ctx** out, const lbm_params* params, const int* obs
     lbm_ctx* c = new lbm_ctx();
     c->prm = *params;
     if (opts) c->opt = *opts;
+    const auto t0 = std::chrono::steady_clock::now();
     if (count_cells(c, obstacles)) { delete c; return 1; }
+    if (env_int("LBM_REPORT", 0) > 1)
+        fprintf(stderr, "create: obstacle count %.4f s\n", std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count());
     *cp = c;
     return 0;
 }
@@ -919,6 +1129,11 @@ int lbm_create(lbm_ctx** out, const lbm_params* params, const int* obstacles, in
         s.dev.ll_down = dn.ll_in;
         s.dev.rec_up = up.rec;     s.dev.rows_up = up.plan.rows;
         s.dev.rec_down = dn.rec;   s.dev.rows_down = dn.plan.rows;
+        for (Slab* o : {&up, &dn}) {
+            check_add(s.device, &s, o->ll_in, sizeof(uint4) * 4 * (size_t)params->nx);
+            check_add(s.device, &s, o->rec, sizeof(uint4) * 2 * 3 * (size_t)(o->plan.rows + 2) * params->nx);
+        }
+        if (!rc) rc = check_upload(s.device);
     }
     if (rc) { lbm_destroy(c); return 1; }
     c->connected = true;
@@ -1097,6 +1312,7 @@ int lbm_sync(lbm_ctx* c)
         CK(cudaMemcpy(&st, s.status, sizeof(int), cudaMemcpyDeviceToHost));
         if (st != 0) return fail("device reported status %d on slab %d (2 = timed out waiting for a neighbouring CTA/GPU)",
                                  st, (int)(&s - &c->slabs[0]) + c->rank0);
+        if (check_report(s.device)) return 1;
     }
     return 0;
 }
@@ -1228,7 +1444,7 @@ int lbm_get_final_state(lbm_ctx* c, float* ux, float* uy, float* u, float* press
     for (Slab& s : c->slabs) {
         CK(cudaSetDevice(s.device));
         const size_t n = (size_t)s.plan.rows * nx;
-        if (!s.fields) CK(cudaMalloc(&s.fields, sizeof(float) * 4 * n));
+        if (!s.fields) CK(dmalloc(&s.fields, sizeof(float) * 4 * n));
         float* dv[4];
         for (int i = 0; i < 4; ++i) dv[i] = host[i] ? s.fields + i * n : nullptr;
         k_final_state<<<(unsigned)((n + 255) / 256), 256, 0, s.stream>>>(s.dev, c->par, c->prm.density, dv[0], dv[1], dv[2], dv[3]);
@@ -1304,7 +1520,11 @@ int lbm_create_rank(lbm_ctx** out, const lbm_params* params, const int* obstacle
     if (!rc) {
         c->size = size; c->nslabs = 1; c->rank0 = rank; c->rank_mode = true;
         c->slabs.resize(1);
+        const auto t0 = std::chrono::steady_clock::now();
+        cudaSetDevice(device);
         rc = configure_engine(c, device);
+        if (env_int("LBM_REPORT", 0) > 1)
+            fprintf(stderr, "create: engine set-up %.4f s\n", std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count());
     }
     if (!rc) rc = slab_create(c, c->slabs[0], rank, device, obstacles);
     if (rc) { lbm_destroy(c); return 1; }
@@ -1359,7 +1579,12 @@ int lbm_rank_connect(lbm_ctx* c, const void* blob_up, const void* blob_down)
         else CK(cudaIpcOpenMemHandle(&s.ipc_rec_down, dn.rec, cudaIpcMemLazyEnablePeerAccess));
         s.dev.rec_up = (uint4*)s.ipc_rec_up;     s.dev.rows_up = up.rows;
         s.dev.rec_down = (uint4*)s.ipc_rec_down; s.dev.rows_down = dn.rows;
+        check_add(s.device, &s, s.ipc_rec_up, sizeof(uint4) * 2 * 3 * (size_t)(up.rows + 2) * c->prm.nx);
+        check_add(s.device, &s, s.ipc_rec_down, sizeof(uint4) * 2 * 3 * (size_t)(dn.rows + 2) * c->prm.nx);
     }
+    check_add(s.device, &s, s.ipc_ll_up, sizeof(uint4) * 4 * (size_t)c->prm.nx);
+    check_add(s.device, &s, s.ipc_ll_down, sizeof(uint4) * 4 * (size_t)c->prm.nx);
+    if (check_upload(s.device)) return 1;
     c->connected = true;
     return 0;
 }

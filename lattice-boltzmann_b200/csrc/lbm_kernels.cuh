@@ -43,6 +43,8 @@ __device__ __forceinline__ TaskGeom task_geom(const SlabDev& d, int2 td, int lan
     return g;
 }
 
+__device__ __forceinline__ unsigned ld_mask(const unsigned char* p) { return chk_ptr(p, 1) ? (unsigned)__ldg(p) : 0u; }
+
 // SM cycle counter that the compiler may not move across barriers or memory operations (profiling)
 __device__ __forceinline__ long long clock_fenced()
 {
@@ -188,7 +190,7 @@ __device__ __forceinline__ float process_task(const SlabDev& d, int par, int2 td
         if (!ll_s) e6 = ld_cg1(src + (6u * ps + g.es));
         if (!ll_n) e7 = ld_cg1(src + (7u * ps + g.en));
     }
-    const unsigned mbyte = __ldg(d.mask + ((unsigned)(g.lr + 1) * (unsigned)d.mask_pitch + ((unsigned)g.xc >> 3)));
+    const unsigned mbyte = ld_mask(d.mask + ((unsigned)(g.lr + 1) * (unsigned)d.mask_pitch + ((unsigned)g.xc >> 3)));
     const unsigned nib = (mbyte >> (g.xc & 4)) & 0xFu;
     if (ll_s | ll_n) {
         const long long t0 = ll_cycles ? clock64() : 0;
@@ -266,7 +268,7 @@ __device__ __forceinline__ void accelerate_task(const SlabDev& d, int par, int2 
     if (!g.active) return;
     float* b = d.buf[par];
     const long long off = (long long)g.rc;
-    const unsigned mbyte = __ldg(d.mask + ((unsigned)(g.lr + 1) * (unsigned)d.mask_pitch + ((unsigned)g.x0 >> 3)));
+    const unsigned mbyte = ld_mask(d.mask + ((unsigned)(g.lr + 1) * (unsigned)d.mask_pitch + ((unsigned)g.x0 >> 3)));
     const unsigned nib = (mbyte >> (g.x0 & 4)) & 0xFu;
     const int ks[6] = {1, 3, 5, 6, 7, 8};
     float4 v[9];
@@ -443,7 +445,8 @@ __global__ void __launch_bounds__(512, 1) lbm_persistent_kernel(SlabDev d, int p
         if (threadIdx.x == 0) {
             double t = 0.0;
             for (int w = 0; w < nw; ++w) t += red[s & 1][w];
-            d.partials[(long long)(step0 + s) * d.num_ctas + b] = t;
+            if (chk_ptr(d.partials + ((long long)(step0 + s) * d.num_ctas + b), 8))
+                d.partials[(long long)(step0 + s) * d.num_ctas + b] = t;
             st_release_gpu(d.flags + b, target + 1u);
         }
         par ^= 1;
@@ -540,7 +543,7 @@ __device__ __forceinline__ DfTask df_task(const SlabDev& d, int id, int lane)
     t.q = t.g.x0 >> 2;
     t.hrow_s = rec_hrow_south<RING>(d, t.g.lr);
     t.hrow_n = rec_hrow_north<RING>(d, t.g.lr);
-    const unsigned mbyte = __ldg(d.mask + ((unsigned)(t.g.lr + 1) * (unsigned)d.mask_pitch + ((unsigned)t.g.xc >> 3)));
+    const unsigned mbyte = ld_mask(d.mask + ((unsigned)(t.g.lr + 1) * (unsigned)d.mask_pitch + ((unsigned)t.g.xc >> 3)));
     t.nib = (mbyte >> (t.g.xc & 4)) & 0xFu;
     return t;
 }
@@ -644,7 +647,8 @@ __device__ __forceinline__ bool df_step(const SlabDev& d, const DfTask& t, int l
         usum = 0.f;
     }
     const double acc = warp_sum((double)usum);
-    if (lane == 0) d.partials[(long long)(step0 + s) * d.num_ctas + t.id] = acc;
+    if (lane == 0 && chk_ptr(d.partials + ((long long)(step0 + s) * d.num_ctas + t.id), 8))
+        d.partials[(long long)(step0 + s) * d.num_ctas + t.id] = acc;
     return true;
 }
 
@@ -696,7 +700,7 @@ __global__ void __launch_bounds__(32, 24) lbm_narrow_kernel(SlabDev d, int par0,
     const int nx = d.nx;
     const bool edge = (lane == 0) || (lane == 31);
     const int xx = (lane == 0) ? (x == 0 ? nx - 1 : x - 1) : (x == nx - 1 ? 0 : x + 1);   // the cell beyond the warp (edge lanes)
-    const bool blocked = (__ldg(d.mask + ((unsigned)(lr + 1) * (unsigned)d.mask_pitch + ((unsigned)x >> 3))) >> (x & 7)) & 1u;
+    const bool blocked = (ld_mask(d.mask + ((unsigned)(lr + 1) * (unsigned)d.mask_pitch + ((unsigned)x >> 3))) >> (x & 7)) & 1u;
     const bool accel_row = (lr == d.accel_lr);
     const unsigned ps = (unsigned)d.ps;
     const unsigned cell = (unsigned)(lr + 1) * (unsigned)nx + (unsigned)x;          // element offset in a SoA plane
@@ -761,10 +765,12 @@ __global__ void __launch_bounds__(32, 24) lbm_narrow_kernel(SlabDev d, int par0,
         } else {                                    // the run's result goes back to the SoA lattice
             float* dst = d.buf[par0 ^ (iters & 1)];
 #pragma unroll
-            for (int k = 0; k < 9; ++k) dst[(unsigned)k * ps + cell] = q[0][k];
+            for (int k = 0; k < 9; ++k)
+                if (chk_ptr(dst + ((unsigned)k * ps + cell), 4)) dst[(unsigned)k * ps + cell] = q[0][k];
         }
         const double acc = warp_sum((double)usum);
-        if (lane == 0) d.partials[(long long)(step0 + s) * d.num_ctas + blockIdx.x] = acc;
+        if (lane == 0 && chk_ptr(d.partials + ((long long)(step0 + s) * d.num_ctas + blockIdx.x), 8))
+            d.partials[(long long)(step0 + s) * d.num_ctas + blockIdx.x] = acc;
     }
 }
 

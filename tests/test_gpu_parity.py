@@ -470,3 +470,56 @@ def test_one_process_per_gpu_equals_single_gpu(lbm, tmp_path, size, grid, steps,
     fn = np.concatenate([np.load(tmp_path / f"cells_{r}.npy") for r in range(size)], axis=1)
     assert np.array_equal(f1, fn)
     np.testing.assert_allclose(np.load(tmp_path / "av.npy"), av1, rtol=3e-7)
+
+
+def _run_py(code, env_extra, timeout=600):
+    import os, subprocess, sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, **env_extra)
+    return subprocess.run([sys.executable, "-c", code], cwd=root, env=env, capture_output=True, text=True, timeout=timeout)
+
+
+def _checked_lib():
+    import os
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    path = os.path.join(root, "lattice-boltzmann_b200", "liblbm_b200_checked.so")
+    if not os.path.exists(path):
+        pytest.skip("liblbm_b200_checked.so not built (make checked)")
+    return path
+
+
+@pytest.mark.parametrize("engine", [1, 3, 4])
+def test_checked_build_catches_an_out_of_range_access(lbm, engine):
+    """compute-sanitizer is not allowed on this GPU pool; the library's self-checking build (-DLBM_CHECKED: every
+    lattice / record / halo access range-checked on the device, lbm_device.cuh) stands in for memcheck.  Proof that
+    the checker fires: with LBM_CHECK_INJECT=1 lattice B is registered one row short, so the legitimate stores to
+    its last haloed row must be reported by lbm_sync."""
+    code = (
+        "import importlib, numpy as np\n"
+        "lbm = importlib.import_module('lattice-boltzmann_b200')\n"
+        "assert lbm.load_library().lbm_checked_build() == 1\n"
+        f"lat = lbm.Lattice(128, 64, 4, 0.1, 0.005, 1.85, np.zeros((64, 128), np.int32), engine={engine})\n"
+        "f = np.full((9, 64, 128), 0.01, np.float32)\n"
+        "try:\n"
+        "    lat.set_cells(f); lat.run(3); lat.sync(); lat.cells()\n"
+        "    print('NOT CAUGHT')\n"
+        "except lbm.LbmError as e:\n"
+        "    print('CAUGHT', e)\n")
+    r = _run_py(code, {"LBM_LIBRARY": _checked_lib(), "LBM_CHECK_INJECT": "1"})
+    assert "CAUGHT checked build:" in r.stdout, r.stdout + r.stderr
+
+
+@pytest.mark.timeout(1500)
+def test_parity_suite_runs_clean_under_the_checked_build(lbm):
+    """The bit-exact oracle tests of every engine (incl. ragged widths, several tasks per warp, split runs and - where
+    the box has them - row slabs over NVLink in both process models), re-run against the self-checking build: no
+    out-of-range / misaligned device access (lbm_sync would fail) and, with all buffers poisoned with NaN bytes
+    before use and recycled through the buffer cache, no result that depends on never-written memory."""
+    import os, subprocess, sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-m", "pytest", "tests", "-m", "gpu", "-x", "-q", "-k",
+                        "random_state_matches or several_tasks_per_warp or engines_and_split or row_slabs or one_process or "
+                        "short_runs or mid_size"],
+                       cwd=root, env=dict(os.environ, LBM_LIBRARY=_checked_lib()), capture_output=True, text=True, timeout=1400)
+    tail = r.stdout[-1500:]
+    assert r.returncode == 0 and " passed" in tail and "failed" not in tail, tail
