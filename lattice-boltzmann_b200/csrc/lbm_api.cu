@@ -817,9 +817,10 @@ int slab_create(lbm_ctx* c, Slab& s, int rank, int device, const int* obst)
         CK(cudaMemset(s.prof, 0, n));
         d.prof = s.prof;
     }
-    // checked build: what this slab's kernels may touch on this device (LBM_CHECK_INJECT=1 registers lattice B one
-    // row short, so that the checker itself can be tested: legitimate accesses to its last row must then be caught)
-    const size_t inject = env_int("LBM_CHECK_INJECT", 0) ? sizeof(float) * (size_t)P.nx : 0;
+    // checked build: what this slab's kernels may touch on this device (LBM_CHECK_INJECT=1 registers lattice B two
+    // rows short - the upper halo row and the last real row of its last plane - so that the checker itself can be
+    // tested: the legitimate stores of f8 to that row must then be caught)
+    const size_t inject = env_int("LBM_CHECK_INJECT", 0) ? 2 * sizeof(float) * (size_t)P.nx : 0;
     check_add(device, &s, s.buf[0], sizeof(float) * 9 * ps);
     check_add(device, &s, s.buf[1], sizeof(float) * 9 * ps - inject);
     check_add(device, &s, s.mask, (size_t)(pl.rows + 2) * pitch);
@@ -862,11 +863,11 @@ void describe(lbm_ctx* c)
 {
     const Slab& s = c->slabs[0];
     snprintf(c->desc, sizeof(c->desc),
-             "engine=%s fp=%s slabs=%d/%d ctas/slab=%d threads/cta=%d tasks/slab=%d tasks/row=%d strips=%d interior=%.0f%%",
+             "engine=%s fp=%s slabs=%d/%d ctas/slab=%d threads/cta=%d tasks/slab=%d tasks/row=%d tasks/warp=%d strips=%d interior=%.0f%%",
              c->engine == 1 ? "persistent-neighbour-sync" : c->engine == 3 ? "dataflow-tagged-records"
              : c->engine == 4 ? "narrow-dataflow-one-cell-per-lane" : "launch-per-step-graph",
              c->strict ? "strict" : "fast",
-             c->nslabs, c->size, s.plan.num_ctas, c->threads, s.plan.num_tasks, s.plan.tpr, s.plan.strips,
+             c->nslabs, c->size, s.plan.num_ctas, c->threads, s.plan.num_tasks, s.plan.tpr, c->engine == 3 ? c->df_k : 0, s.plan.strips,
              100.0 * lbm::interior_fraction(s.plan));
 }
 

@@ -492,8 +492,8 @@ def _checked_lib():
 def test_checked_build_catches_an_out_of_range_access(lbm, engine):
     """compute-sanitizer is not allowed on this GPU pool; the library's self-checking build (-DLBM_CHECKED: every
     lattice / record / halo access range-checked on the device, lbm_device.cuh) stands in for memcheck.  Proof that
-    the checker fires: with LBM_CHECK_INJECT=1 lattice B is registered one row short, so the legitimate stores to
-    its last haloed row must be reported by lbm_sync."""
+    the checker fires: with LBM_CHECK_INJECT=1 lattice B is registered two rows short, so the legitimate stores to
+    the last real row of its last plane must be reported by lbm_sync."""
     code = (
         "import importlib, numpy as np\n"
         "lbm = importlib.import_module('lattice-boltzmann_b200')\n"
