@@ -94,9 +94,12 @@ template <class T> cudaError_t dmalloc(T** out, size_t bytes)
 {
     cudaError_t e = dmalloc_bytes((void**)out, bytes);
 #ifdef LBM_CHECKED
-    if (e == cudaSuccess) e = cudaMemset(*out, 0xFF, std::max<size_t>(bytes, 1));
-    if (e == cudaSuccess) e = cudaDeviceSynchronize();
+    const bool poison = !(getenv("LBM_POISON") && atoi(getenv("LBM_POISON")) == 0);
+#else
+    const bool poison = getenv("LBM_POISON") && atoi(getenv("LBM_POISON")) != 0;   // any build can be asked to
 #endif
+    if (poison && e == cudaSuccess) e = cudaMemset(*out, 0xFF, std::max<size_t>(bytes, 1));
+    if (poison && e == cudaSuccess) e = cudaDeviceSynchronize();
     return e;
 }
 

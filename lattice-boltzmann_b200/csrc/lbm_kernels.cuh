@@ -100,7 +100,7 @@ __device__ __noinline__ HaloRow ll_pull_slow(const uint4* pq, const uint4* pw, c
         // give up warp-uniformly (another CTA failed, or the neighbour never arrives)
         const bool late = clock64() - t0 > kSpinLimitCycles;
         if (late) atomicExch(status, 2);
-        if (__any_sync(0xffffffffu, late || *(volatile int*)status != 0)) break;
+        if (__any_sync(0xffffffffu, late || ld_status(status) != 0)) break;
         __nanosleep(40);
     }
     return h;
@@ -369,7 +369,7 @@ __device__ __forceinline__ void wait_deps(const SlabDev& d, int dep_lo, int dep_
         for (;;) {
             const unsigned v = ld_acquire_gpu(f);
             if ((int)(v - target) >= 0) break;
-            if (*(volatile int*)d.status != 0) break;
+            if (ld_status(d.status) != 0) break;
             if (clock64() - t0 > kSpinLimitCycles) { atomicExch(d.status, 2); break; }
             __nanosleep(20);
         }
@@ -601,7 +601,7 @@ __device__ __forceinline__ bool df_step(const SlabDev& d, const DfTask& t, int l
         if (tries == 0) t0 = clock64();
         const bool late = clock64() - t0 > kSpinLimitCycles;
         if (late) atomicExch(d.status, 2);
-        if (__any_sync(full, late || *(volatile int*)d.status != 0)) return false;
+        if (__any_sync(full, late || ld_status(d.status) != 0)) return false;
     }
     const float4 c0 = cv[0], c1 = cv[1], c3 = cv[2], s2 = sv[0], s5 = sv[1], s6 = sv[2], n4 = nv[0], n7 = nv[1], n8 = nv[2];
 
@@ -736,7 +736,7 @@ __global__ void __launch_bounds__(32, 24) lbm_narrow_kernel(SlabDev d, int par0,
             if (tries == 0) t0 = clock64();
             const bool late = clock64() - t0 > kSpinLimitCycles;
             if (late) atomicExch(d.status, 2);
-            if (__any_sync(full, late || *(volatile int*)d.status != 0)) return;
+            if (__any_sync(full, late || ld_status(d.status) != 0)) return;
         }
         // pull (d2q9-bgk.c:315): f1,f5,f8 come from the west cell, f3,f6,f7 from the east cell
         float p[9];

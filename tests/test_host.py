@@ -177,3 +177,33 @@ def test_checker_restatement_matches_reference_checker(tmp_path, golden):
         b = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "check.py"), *args], capture_output=True, text=True)
         assert a.returncode == b.returncode == expect
         assert a.stdout == b.stdout
+
+
+@pytest.mark.parametrize("lib", ["liblbm_b200.so", "liblbm_b200_checked.so"])
+def test_tagged_record_accesses_are_never_narrowed_in_sass(lib):
+    """A tagged record {v,v,v,tag} must be read and written by ONE 16-byte access, or a reader can pair a new tag with
+    an old payload.  ptxas does not treat ld.relaxed.sys.b128 as indivisible: where only some words are used it
+    narrowed the load, and in the self-checking build it split it into two 32-bit loads (payload first, tag second),
+    which broke engine 3 there.  The accessors are .volatile now (lbm_device.cuh); this test reads the SASS of every
+    timestep kernel of every build: all system-scope strong accesses - which only the records use - are 128 bits wide."""
+    import shutil
+    path = os.path.join(ROOT, "lattice-boltzmann_b200", lib)
+    if not os.path.exists(path) or not shutil.which("cuobjdump"):
+        pytest.skip("needs the built library and cuobjdump")
+    sass = subprocess.run(["cuobjdump", "-sass", path], capture_output=True, text=True, check=True).stdout
+    fn, per_fn = None, {}
+    for line in sass.splitlines():
+        m = re.search(r"Function : (\S+)", line)
+        if m:
+            fn = m.group(1)
+            continue
+        m = re.search(r"\b(LDG|STG)\.E((?:\.[A-Z0-9]+)*)\.STRONG\.SYS\b", line)
+        if m and fn and re.search(r"lbm_(persistent|dataflow|narrow|step)_kernel", fn):
+            per_fn.setdefault(fn, []).append(m.group(1) + m.group(2))
+    assert per_fn, "no timestep kernels found in the SASS"
+    total = 0
+    for fn, ops in per_fn.items():
+        narrow = [o for o in ops if not o.endswith(".128")]
+        assert not narrow, f"{fn}: narrowed record accesses {sorted(set(narrow))}"
+        total += len(ops)
+    assert total > 100
