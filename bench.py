@@ -220,10 +220,9 @@ def make_lattice(lbm, torch, dist, case, cap, rank, world, **kw):
 
 
 def close_lattice(lat, world, dist):
+    """Teardown as include/lbm_b200.h prescribes for one process per GPU: disconnect, destroy - no barrier."""
     if world > 1:
-        lat.sync()
-        lat.rank_disconnect()        # CUDA IPC: importers unmap before the exporter frees
-        dist.barrier()
+        lat.rank_disconnect()
     lat.close()
 
 
@@ -505,6 +504,13 @@ def main():
     if args.warmup < 3:
         args.warmup = 3
 
+    # stdout carries exactly ONE line, the JSON record: file descriptor 1 is pointed at stderr for the rest of the run
+    # (NCCL prints its version banner and NCCL_DEBUG output on stdout from C; NCCL_DEBUG itself is left alone so that
+    # whoever launched the bench can read NCCL's log), and the record is written to the saved descriptor at the end.
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
+
     import torch
     lbm = importlib.import_module("lattice-boltzmann_b200")
     if not torch.cuda.is_available() or lbm.device_count() < 1:
@@ -513,9 +519,6 @@ def main():
     torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", "0")))
     if world > 1:
         import torch.distributed as dist
-        # stdout carries exactly one JSON line: NCCL's own log (NCCL_DEBUG=VERSION/WARN/INFO), if asked for, goes to stderr
-        if os.environ.get("NCCL_DEBUG") and not os.environ.get("NCCL_DEBUG_FILE"):
-            os.environ["NCCL_DEBUG_FILE"] = "/dev/stderr"
         dist.init_process_group("nccl", device_id=torch.device("cuda", torch.cuda.current_device()))
     if world != args.gpus:
         raise SystemExit(f"bench.py: --gpus {args.gpus} needs {args.gpus} ranks (torchrun), got WORLD_SIZE={world}")
@@ -526,7 +529,7 @@ def main():
     parity = None if args.no_parity else parity_check(lbm, torch, dist, grid, rank, world)
     if parity is not None and not parity["ok"]:
         if rank == 0:
-            print(json.dumps({"error": "parity_check failed", "parity_check": parity}), flush=True)
+            os.write(json_fd, (json.dumps({"error": "parity_check failed", "parity_check": parity}) + "\n").encode())
         return 1
     res = time_resident(lbm, torch, grid, iters, args.steps, args.warmup, rank, world, dist, scratch)
     e2e = time_e2e(lbm, torch, grid, iters, max(1, min(args.steps, 3)), rank, world, dist)
@@ -586,7 +589,7 @@ def main():
             except Exception as e:
                 line["cpu_baseline"] = {"value": None, "unit": "GLUPS", "cores": host_cores(), "kind": "reference",
                                         "sample": f"failed: {str(e)[:160]}"}
-        print(json.dumps(line), flush=True)
+        os.write(json_fd, (json.dumps(line) + "\n").encode())
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()

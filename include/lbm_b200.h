@@ -209,11 +209,15 @@ int lbm_create_rank(lbm_ctx** out, const lbm_params* params, const int* obstacle
                     int rank, int size, int device, const lbm_options* opts);
 int lbm_rank_export(lbm_ctx* ctx, void* blob /* LBM_IPC_BLOB_BYTES */);
 int lbm_rank_connect(lbm_ctx* ctx, const void* blob_up, const void* blob_down);
-/* Teardown order in this mode (CUDA IPC requires importers to unmap before the exporter frees):
- *   every rank: lbm_rank_disconnect (waits for the local kernel, unmaps the neighbours' slots);
- *   host barrier across the ranks;  every rank: lbm_destroy.
- * No kernel can still be writing into a slab at that point: a slab whose own kernel has finished has consumed
- * every halo record a neighbour will send it (the last timestep of a run pushes nothing). */
+/* Teardown in this mode: every rank calls lbm_rank_disconnect (waits for the local kernel, forgets the neighbours'
+ * pointers) and then lbm_destroy; no barrier between the ranks is needed:
+ *  - no kernel can still be writing into a slab whose own kernel has finished: it has consumed every halo record a
+ *    neighbour will send it (the last timestep of a run pushes nothing);
+ *  - buffers whose IPC handle was exported are never returned to the driver while the process lives (they wait in the
+ *    buffer cache for the next context of the same shape), and the importers keep their mappings open in a per-process
+ *    cache, so a neighbour's mapping never outlives the memory behind it.
+ * lbm_trim_cache is the exception: in this mode call it on all ranks only after all ranks have destroyed their
+ * contexts (a host barrier), because it closes the mappings and frees the exported buffers. */
 int lbm_rank_disconnect(lbm_ctx* ctx);
 /* 1/free_cells by the rule of params.obstacle_lines (for the caller's final scaling). */
 float lbm_inv_free_cells(const lbm_ctx* ctx);

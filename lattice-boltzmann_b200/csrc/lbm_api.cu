@@ -10,6 +10,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <map>
 #include <mutex>
 #include <stdexcept>
 #include <string>
@@ -54,6 +55,10 @@ struct DevCache {
     std::mutex mu;
     std::vector<Entry> idle;                                          // oldest first
     std::unordered_map<void*, std::pair<int, size_t>> live;           // handed out, not yet returned
+    std::unordered_map<void*, bool> exported;                         // buffers whose CUDA IPC handle went to other processes:
+                                                                      // never returned to the driver before lbm_trim_cache,
+                                                                      // because an importer may still hold a mapping
+    std::map<std::pair<int, std::string>, void*> ipc_open;            // (device, handle bytes) -> mapping opened in THIS process
     size_t idle_bytes = 0;
     static size_t limit()
     {
@@ -116,14 +121,16 @@ void dfree(void* p)
             const DevCache::Entry e{it->second.first, it->second.second, p};
             g_cache.live.erase(it);
             const size_t lim = DevCache::limit();
-            if (e.bytes > lim) evict.push_back(e);
+            const bool sticky = g_cache.exported.count(p) != 0;
+            if (e.bytes > lim && !sticky) evict.push_back(e);
             else {
                 g_cache.idle.push_back(e);
                 g_cache.idle_bytes += e.bytes;
-                while (g_cache.idle_bytes > lim && !g_cache.idle.empty()) {
-                    evict.push_back(g_cache.idle.front());
-                    g_cache.idle_bytes -= g_cache.idle.front().bytes;
-                    g_cache.idle.erase(g_cache.idle.begin());
+                for (size_t i = 0; g_cache.idle_bytes > lim && i < g_cache.idle.size();) {
+                    if (g_cache.exported.count(g_cache.idle[i].p)) { ++i; continue; }     // oldest first, exported ones stay
+                    evict.push_back(g_cache.idle[i]);
+                    g_cache.idle_bytes -= g_cache.idle[i].bytes;
+                    g_cache.idle.erase(g_cache.idle.begin() + (long)i);
                 }
             }
         }
@@ -136,6 +143,26 @@ void dfree(void* p)
         cudaFree(e.p);
     }
     cudaSetDevice(cur);
+}
+
+// CUDA IPC mappings of the ring neighbours' buffers are opened once per (device, handle) and kept: with the buffer
+// cache the same allocations come back context after context, and cudaIpcOpen/CloseMemHandle cost milliseconds each.
+cudaError_t ipc_open_cached(void** out, const cudaIpcMemHandle_t& h)
+{
+    int dev = 0;
+    cudaGetDevice(&dev);
+    const std::pair<int, std::string> key(dev, std::string((const char*)&h, sizeof(h)));
+    std::lock_guard<std::mutex> g(g_cache.mu);
+    auto it = g_cache.ipc_open.find(key);
+    if (it != g_cache.ipc_open.end()) { *out = it->second; return cudaSuccess; }
+    const cudaError_t e = cudaIpcOpenMemHandle(out, h, cudaIpcMemLazyEnablePeerAccess);
+    if (e == cudaSuccess) g_cache.ipc_open[key] = *out;
+    return e;
+}
+void mark_exported(void* p)
+{
+    std::lock_guard<std::mutex> g(g_cache.mu);
+    g_cache.exported[p] = true;
 }
 
 // ---- checked build: the per-device table of valid address ranges (see lbm_device.cuh) ---------------------
@@ -618,10 +645,7 @@ void slab_free(Slab& s)
     check_remove(&s);
     check_upload(s.device);
     if (s.graph) cudaGraphExecDestroy(s.graph);
-    if (s.ipc_ll_up) cudaIpcCloseMemHandle(s.ipc_ll_up);
-    if (s.ipc_ll_down && s.ipc_ll_down != s.ipc_ll_up) cudaIpcCloseMemHandle(s.ipc_ll_down);
-    if (s.ipc_rec_up) cudaIpcCloseMemHandle(s.ipc_rec_up);
-    if (s.ipc_rec_down && s.ipc_rec_down != s.ipc_rec_up) cudaIpcCloseMemHandle(s.ipc_rec_down);
+    // (CUDA IPC mappings of the neighbours' buffers stay open in the process-wide cache, see ipc_open_cached)
     const double t1 = now();
     dfree(s.buf[0]);
     const double t2 = now();
@@ -1041,13 +1065,17 @@ int lbm_selftest_records(int writer_device, int reader_device, int sweeps, int m
 int lbm_trim_cache(void)
 {
     std::vector<DevCache::Entry> all;
+    std::map<std::pair<int, std::string>, void*> maps;
     {
         std::lock_guard<std::mutex> g(g_cache.mu);
         all.swap(g_cache.idle);
         g_cache.idle_bytes = 0;
+        maps.swap(g_cache.ipc_open);
+        for (const auto& e : all) g_cache.exported.erase(e.p);
     }
     int cur = 0;
     cudaGetDevice(&cur);
+    for (const auto& m : maps) { cudaSetDevice(m.first.first); cudaIpcCloseMemHandle(m.second); }
     for (const auto& e : all) { cudaSetDevice(e.dev); cudaFree(e.p); }
     cudaSetDevice(cur);
     cudaGetLastError();
@@ -1547,8 +1575,8 @@ int lbm_rank_export(lbm_ctx* c, void* blob)
     memset(&b, 0, sizeof(b));
     b.magic = 0x4C424D32u;  // "LBM2"
     b.rank = c->rank0; b.size = c->size; b.nx = c->prm.nx; b.rows = s.plan.rows; b.engine = c->engine;
-    if (c->size > 1) CK(cudaIpcGetMemHandle(&b.ll_in, s.ll_in));
-    if (c->size > 1 && s.rec) CK(cudaIpcGetMemHandle(&b.rec, s.rec));
+    if (c->size > 1) { CK(cudaIpcGetMemHandle(&b.ll_in, s.ll_in)); mark_exported(s.ll_in); }
+    if (c->size > 1 && s.rec) { CK(cudaIpcGetMemHandle(&b.rec, s.rec)); mark_exported(s.rec); }
     memset(blob, 0, LBM_IPC_BLOB_BYTES);
     memcpy(blob, &b, sizeof(b));
     return 0;
@@ -1572,15 +1600,15 @@ int lbm_rank_connect(lbm_ctx* c, const void* blob_up, const void* blob_down)
     if (up.engine != c->engine || dn.engine != c->engine)
         return fail("lbm_rank_connect: neighbours run engines %d / %d, this rank engine %d", up.engine, dn.engine, c->engine);
     const bool same = (r_up == r_dn);   // size == 2: both neighbours are the same process
-    CK(cudaIpcOpenMemHandle(&s.ipc_ll_up, up.ll_in, cudaIpcMemLazyEnablePeerAccess));
+    CK(ipc_open_cached(&s.ipc_ll_up, up.ll_in));
     if (same) s.ipc_ll_down = s.ipc_ll_up;
-    else CK(cudaIpcOpenMemHandle(&s.ipc_ll_down, dn.ll_in, cudaIpcMemLazyEnablePeerAccess));
+    else CK(ipc_open_cached(&s.ipc_ll_down, dn.ll_in));
     s.dev.ll_up = (uint4*)s.ipc_ll_up;
     s.dev.ll_down = (uint4*)s.ipc_ll_down;
     if (s.rec) {
-        CK(cudaIpcOpenMemHandle(&s.ipc_rec_up, up.rec, cudaIpcMemLazyEnablePeerAccess));
+        CK(ipc_open_cached(&s.ipc_rec_up, up.rec));
         if (same) s.ipc_rec_down = s.ipc_rec_up;
-        else CK(cudaIpcOpenMemHandle(&s.ipc_rec_down, dn.rec, cudaIpcMemLazyEnablePeerAccess));
+        else CK(ipc_open_cached(&s.ipc_rec_down, dn.rec));
         s.dev.rec_up = (uint4*)s.ipc_rec_up;     s.dev.rows_up = up.rows;
         s.dev.rec_down = (uint4*)s.ipc_rec_down; s.dev.rows_down = dn.rows;
         check_add(s.device, &s, s.ipc_rec_up, sizeof(uint4) * 2 * 3 * (size_t)(up.rows + 2) * c->prm.nx);
@@ -1600,10 +1628,7 @@ int lbm_rank_disconnect(lbm_ctx* c)
     if (lbm_sync(c)) return 1;                       // my kernel may still be pushing into the mappings
     Slab& s = c->slabs[0];
     CK(cudaSetDevice(s.device));
-    if (s.ipc_ll_up) CK(cudaIpcCloseMemHandle(s.ipc_ll_up));
-    if (s.ipc_ll_down && s.ipc_ll_down != s.ipc_ll_up) CK(cudaIpcCloseMemHandle(s.ipc_ll_down));
-    if (s.ipc_rec_up) CK(cudaIpcCloseMemHandle(s.ipc_rec_up));
-    if (s.ipc_rec_down && s.ipc_rec_down != s.ipc_rec_up) CK(cudaIpcCloseMemHandle(s.ipc_rec_down));
+    // the mappings themselves stay open in the process-wide cache (ipc_open_cached); lbm_trim_cache closes them
     s.ipc_ll_up = s.ipc_ll_down = s.ipc_rec_up = s.ipc_rec_down = nullptr;
     s.dev.ll_up = s.dev.ll_down = s.dev.rec_up = s.dev.rec_down = nullptr;
     c->connected = false;

@@ -442,9 +442,9 @@ def _rank_worker(rank, size, port, grid, steps, out_dir, engine):
     np.save(os.path.join(out_dir, f"cells_{rank}.npy"), f)
     if rank == 0:
         np.save(os.path.join(out_dir, "av.npy"), av)
-    lat.rank_disconnect()           # CUDA IPC: importers unmap, then a barrier, then the exporters free
-    dist.barrier()
+    lat.rank_disconnect()           # teardown as lbm_b200.h prescribes: disconnect, destroy; no barrier between ranks
     lat.close()
+    dist.barrier()
     dist.destroy_process_group()
 
 
