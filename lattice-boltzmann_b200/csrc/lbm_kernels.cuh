@@ -590,9 +590,16 @@ __device__ __forceinline__ bool df_step(const SlabDev& d, const DfTask& t, int l
     float4 cv[3], sv[3], nv[3];      // (f0,f1,f3) of the row; (f2,f5,f6) of the south row; (f4,f7,f8) of the north row
     float w1 = 0.f, w5 = 0.f, w8 = 0.f, e3 = 0.f, e6 = 0.f, e7 = 0.f;
     long long t0 = 0;
+#ifdef LBM_DF_PROBE   // dev aid (tools/probes/df_split.py): where does a dataflow step's time go?  needs LBM_PROFILE=1
+    const long long pr0 = clock_fenced();
+    int pr_tries = 0;
+#endif
     // all loads of the three groups go out back to back and are voted on ONCE; polling the groups one by
     // one measured slower (three dependent votes on the fast path)
     for (int tries = 0;; ++tries) {
+#ifdef LBM_DF_PROBE
+        pr_tries = tries;
+#endif
         bool ok = rec_take<0>(d, rec_group(d, rp, g.lr + 1, kRecHorizontal), g, tag, cv, w1, e3);
         ok = rec_take<0>(d, rec_group(d, rp, t.hrow_s, kRecNorthbound), g, tag, sv, w5, e6) && ok;
         ok = rec_take<1>(d, rec_group(d, rp, t.hrow_n, kRecSouthbound), g, tag, nv, w8, e7) && ok;
@@ -604,6 +611,9 @@ __device__ __forceinline__ bool df_step(const SlabDev& d, const DfTask& t, int l
         if (__any_sync(full, late || ld_status(d.status) != 0)) return false;
     }
     const float4 c0 = cv[0], c1 = cv[1], c3 = cv[2], s2 = sv[0], s5 = sv[1], s6 = sv[2], n4 = nv[0], n7 = nv[1], n8 = nv[2];
+#ifdef LBM_DF_PROBE
+    const long long pr1 = clock_fenced();
+#endif
 
     // ---- lane-crossing elements by shuffle, pulled populations (d2q9-bgk.c:315): as process_task
     float x;
@@ -646,6 +656,13 @@ __device__ __forceinline__ bool df_step(const SlabDev& d, const DfTask& t, int l
     } else {
         usum = 0.f;
     }
+#ifdef LBM_DF_PROBE
+    if (d.prof && lane == 0) {
+        long long* o = d.prof + (long long)t.id * kMaxWarps * 4;
+        const long long pr2 = clock_fenced();
+        o[0] += pr1 - pr0; o[1] += pr_tries; o[2] += pr2 - pr1; o[3] += 1;
+    }
+#endif
     const double acc = warp_sum((double)usum);
     if (lane == 0 && chk_ptr(d.partials + ((long long)(step0 + s) * d.num_ctas + t.id), 8))
         d.partials[(long long)(step0 + s) * d.num_ctas + t.id] = acc;

@@ -1,5 +1,5 @@
 #!/usr/bin/env python3
-"""Turns the ncu artefacts of tools/profile_r01.sh (gpurun_out/) into the tracked summaries under profiles/.
+"""Turns the ncu artefacts of tools/profile_r01.sh / profile_r02.sh (gpurun_out/) into the tracked summaries under profiles/.
     python tools/ncu_summary.py r01        # runs here (no GPU needed): ncu -i <rep> --page raw --csv
 """
 import csv
@@ -48,7 +48,7 @@ def full_summary(tag, grid, steps, kind="persistent", config="1:256:2:1"):
     cells = nx * ny
     lines = [f"# {tag} — ncu --set full of lbm_{kind}_kernel<strict> on {grid} ({steps} timesteps in one launch)", "",
              f"Command: `python tools/explore.py --grid {grid} --steps {steps} --reps 1 --configs {config}` (2nd launch captured, "
-             f"`-s 1 -c 1`), ncu --set full --clock-control none --import-source on (tools/profile_r01.sh). "
+             f"`-s 1 -c 1`), ncu --set full --clock-control none --import-source on (tools/profile_{tag}.sh). "
              f"Report: gpurun_out/prof_{kind}_{grid}.ncu-rep (scratch).", "",
              f"kernel: `{m['Kernel Name'][0]}`  grid {m.get('Grid Size', ('?',))[0]} block {m.get('Block Size', ('?',))[0]}", "",
              "| metric | value | unit |", "|---|---|---|"]
@@ -94,7 +94,8 @@ def launch_list(tag):
         n, t = agg.get(key, (0, 0.0))
         agg[key] = (n + 1, t + ms)
     tot = sum(t for _, t in agg.values())
-    lines = [f"# {tag} — launch list of `python bench.py --steps 1 --warmup 3 --iters 300 --no-cpu-baseline`", "",
+    cmd = "python bench.py --steps 1 --warmup 3 --iters 300 --no-cpu-baseline" + ("" if tag == "r01" else " --no-also")
+    lines = [f"# {tag} — launch list of `{cmd}`", "",
              f"ncu --metrics gpu__time_duration.sum --clock-control none (cold-cache, serialised: compare SHARES). "
              f"Raw CSV: {tag}_launches_bench.csv", "", "| kernel | launches | grid | block | total ms | share |", "|---|---|---|---|---|---|"]
     for (name, g, b), (n, t) in sorted(agg.items(), key=lambda kv: -kv[1][1]):
