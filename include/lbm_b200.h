@@ -58,10 +58,12 @@ typedef struct lbm_options {
     int engine;         /* 0 = auto (4 or 3 where they apply, else 1); 1 = persistent neighbour-synchronised
                            kernel; 2 = one launch per timestep (CUDA-graph replayed, single slab); 3 = dataflow
                            over tagged records: one resident warp per 128-cell task (or per 2-3 of them), slabs
-                           of at most ~7000 tasks (... 512x512, 1024x768); 4 = the same with 32-cell tasks, one
-                           cell per lane: slabs of at most ~4700 such tasks (128x128 ... 256x256), nx % 32 == 0.
-                           Engines 3 and 4 also run row slabs on several GPUs (records of the edge rows are
-                           stored straight into the ring neighbour's record lattice). */
+                           of at most ~7000 tasks (... 512x512, 1024x768); 4 = dataflow with one resident CTA per
+                           ROW, one cell per thread: nx % 32 == 0, nx <= 1024, all rows of a slab resident (up to
+                           1184 rows of 128 cells, 592 of 256, 148 of 1024); auto takes it for rows of up to 256
+                           cells (the check grids 128x128, 128x256, 256x256).  Engines 3 and 4 also run row slabs
+                           on several GPUs (records of the edge rows are stored straight into the ring
+                           neighbour's record lattice). */
     int first_device;   /* first CUDA device ordinal used (single-process multi-GPU uses
                            first_device .. first_device+ngpus-1) */
 } lbm_options;

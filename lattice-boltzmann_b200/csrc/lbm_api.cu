@@ -483,10 +483,10 @@ const void* dataflow_pick(bool strict, bool multi)
 }
 const void* dataflow_fn(bool strict, bool multi, bool ring) { return ring ? dataflow_pick<true>(strict, multi) : dataflow_pick<false>(strict, multi); }
 
-const void* narrow_fn(bool strict, bool ring)
+const void* row_fn(bool strict, bool ring)
 {
-    if (ring) return strict ? (const void*)lbm::lbm_narrow_kernel<true, true> : (const void*)lbm::lbm_narrow_kernel<false, true>;
-    return strict ? (const void*)lbm::lbm_narrow_kernel<true, false> : (const void*)lbm::lbm_narrow_kernel<false, false>;
+    if (ring) return strict ? (const void*)lbm::lbm_row_kernel<true, true> : (const void*)lbm::lbm_row_kernel<false, true>;
+    return strict ? (const void*)lbm::lbm_row_kernel<true, false> : (const void*)lbm::lbm_row_kernel<false, false>;
 }
 
 // LBM_PROFILE=1 selects the instantiations that carry the per-warp cycle counters
@@ -680,25 +680,25 @@ int configure_engine(lbm_ctx* c, int device)
     c->engine = c->opt.engine ? c->opt.engine : env_int("LBM_ENGINE", 0);
     if (c->engine < 0 || c->engine > 4) return fail("unknown engine %d", c->engine);
     if (c->engine == 2 && c->size > 1) return fail("engine 2 (launch per timestep) supports a single slab only");
-    // The dataflow engines (3: 128-cell tasks, 4: 32-cell tasks) need every task of a slab on its own resident
-    // warp (one warp per block) and keep one partial sum per task and step; auto picks them whenever the slab
-    // is small enough for both.  Every rank must decide alike, so the decision uses the LARGEST slab of the ring
-    // (rank 0's: ceil(ny / size) rows).
+    // The dataflow engines (3: one warp per 128-cell task, 4: one CTA per row) need every task of a slab resident
+    // for the whole run and keep one partial sum per warp and step; auto picks them whenever the slab is small enough
+    // for both.  Every rank must decide alike, so the decision uses the LARGEST slab of the ring (rank 0's:
+    // ceil(ny / size) rows).
     const bool ring = c->size > 1;
     const int rows_max = (c->prm.ny + c->size - 1) / c->size;
     const long long tasks = (long long)((c->prm.nx + lbm::kTaskCells - 1) / lbm::kTaskCells) * rows_max;
-    const long long ntasks = (c->prm.nx % 32 == 0) ? (long long)(c->prm.nx / 32) * rows_max : -1;
+    const long long warps_row = (c->prm.nx % 32 == 0 && c->prm.nx <= 1024) ? (long long)(c->prm.nx / 32) * rows_max : -1;
     // resident warps: the smaller of the two instantiations' occupancies, so that whichever is launched
     // (one task per warp, or several) passes the cooperative launch's co-residency check
     int occ3 = 0, occ3m = 0, occ4 = 0;
     CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ3, dataflow_fn(c->strict, false, ring), 32, 0));
     CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ3m, dataflow_fn(c->strict, true, ring), 32, 0));
-    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ4, narrow_fn(c->strict, ring), 32, 0));
-    const long long warps3 = (long long)std::min(occ3, occ3m) * sms, warps4 = (long long)occ4 * sms;
+    if (warps_row > 0) CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ4, row_fn(c->strict, ring), c->prm.nx, 0));
+    const long long warps3 = (long long)std::min(occ3, occ3m) * sms;
     const long long steps = std::max(c->prm.max_iters, 1);
     const bool mem3 = tasks * steps * (long long)sizeof(double) <= (2LL << 30);
-    const bool mem4 = ntasks * steps * (long long)sizeof(double) <= (2LL << 30);
-    const bool fits4 = ntasks > 0 && ntasks <= warps4 && mem4;
+    const bool mem4 = warps_row * steps * (long long)sizeof(double) <= (2LL << 30);
+    const bool fits4 = occ4 > 0 && rows_max <= (long long)occ4 * sms && mem4;
     // engine 3: a warp owns 1 task, or several consecutive ones when the slab has more tasks than resident warps.
     // Measured (profiles/r01_small_lattice.md): 2 per warp beats engine 1 by 2.3x (1024x512), 3 per warp by 1.4x
     // (1024x768: 82 vs 59 GLUPS), 4 per warp loses to it (1024x896: 74 vs 85, 1024x1024: 73 vs 98) - auto stops
@@ -714,12 +714,11 @@ int configure_engine(lbm_ctx* c, int device)
         c->df_k = k;
     }
     if (c->engine == 4 && !fits4)
-        return fail("engine 4 (one cell per lane) needs nx %% 32 == 0, slabs of at most %lld 32-cell tasks (the largest here "
-                    "has %lld) and at most 2 GiB of per-step partial sums", warps4, ntasks);
-    // auto never takes engine 4: measured (profiles/r02_small_lattice.md) it ties engine 3 on 128x128 (1.50 vs 1.52 us
-    // per step) and loses from 256x256 on (1.77 vs 1.65; 512x256: 4.72 vs 2.13) - a step is bounded by the L2 hop
-    // between SMs (530-1300 cycles one way), not by the instructions of one warp
-    if (c->engine == 0) c->engine = fits3 ? 3 : 1;
+        return fail("engine 4 (one CTA per row) needs nx %% 32 == 0, nx <= 1024, slabs of at most %lld rows (the largest here "
+                    "has %d) and at most 2 GiB of per-step partial sums", (long long)occ4 * sms, rows_max);
+    // auto: the row engine where it measured faster than engine 3 (rows of up to 256 cells: 128x128 1.17 vs 1.58 us per
+    // step, 256x256 1.52 vs 1.68; 512x256 loses, 2.34 vs 2.16 - profiles/r02_small_lattice.md), then engine 3, then 1
+    if (c->engine == 0) c->engine = (fits4 && c->prm.nx <= 256) ? 4 : fits3 ? 3 : 1;
     c->threads = c->opt.threads_per_cta ? c->opt.threads_per_cta : env_int("LBM_THREADS", 256);
     if (c->threads % 32 || c->threads < 32 || c->threads > 512) return fail("threads_per_cta must be a multiple of 32 in [32,512]");
     int per_sm = c->opt.ctas_per_sm ? c->opt.ctas_per_sm : env_int("LBM_CTAS_PER_SM", 2);
@@ -731,7 +730,7 @@ int configure_engine(lbm_ctx* c, int device)
     if (occ < 1) return fail("persistent kernel does not fit on an SM with %d threads", c->threads);
     per_sm = std::max(1, std::min(per_sm, occ));
     c->ctas_budget = sms * per_sm;
-    if (c->engine == 3 || c->engine == 4) {      // one block of one warp per task (engine 3: or per df_k tasks)
+    if (c->engine >= 3) {                        // one block of one warp per task (engine 3: or per df_k tasks), or per row
         c->threads = 32;
         c->ctas_budget = (int)tasks;             // the plan keeps one "CTA" per wide task; engine 4 sizes its own partials
         return 0;
@@ -764,8 +763,8 @@ int slab_create(lbm_ctx* c, Slab& s, int rank, int device, const int* obst)
     if (9 * ps >= (1LL << 32))
         return fail("slab of %d rows x %d cells is too large for 32-bit lattice offsets (9*(rows+2)*nx must be < 2^32); "
                     "use more GPUs", pl.rows, P.nx);
-    // slots of per-step partial sums: one per persistent CTA (engine 1), per wide task (3) or per narrow task (4)
-    const int G = (c->engine == 4) ? pl.rows * (P.nx / 32) : pl.num_ctas;
+    // slots of per-step partial sums: one per persistent CTA (engine 1), per task (3) or per warp of a row CTA (4)
+    const int G = (c->engine >= 4) ? pl.rows * (P.nx / 32) : pl.num_ctas;
     const int pitch = ((P.nx + 7) / 8 + 15) / 16 * 16;
 
     for (int i = 0; i < 2; ++i) CK(dmalloc(&s.buf[i], sizeof(float) * 9 * ps));
@@ -781,7 +780,7 @@ int slab_create(lbm_ctx* c, Slab& s, int rank, int device, const int* obst)
         CK(dmalloc(&s.ll_in, sizeof(uint4) * 4 * (size_t)P.nx));
         CK(cudaMemsetAsync(s.ll_in, 0, sizeof(uint4) * 4 * (size_t)P.nx, s.stream));
     }
-    if (c->engine == 3 || c->engine == 4) {  // tag 0 = never written
+    if (c->engine >= 3) {  // tag 0 = never written
         const size_t bytes = sizeof(uint4) * 2 * 3 * (size_t)(pl.rows + 2) * P.nx;
         CK(dmalloc(&s.rec, bytes));
         CK(cudaMemsetAsync(s.rec, 0, bytes, s.stream));
@@ -892,7 +891,7 @@ void describe(lbm_ctx* c)
     snprintf(c->desc, sizeof(c->desc),
              "engine=%s fp=%s slabs=%d/%d ctas/slab=%d threads/cta=%d tasks/slab=%d tasks/row=%d tasks/warp=%d strips=%d interior=%.0f%%",
              c->engine == 1 ? "persistent-neighbour-sync" : c->engine == 3 ? "dataflow-tagged-records"
-             : c->engine == 4 ? "narrow-dataflow-one-cell-per-lane" : "launch-per-step-graph",
+             : c->engine == 4 ? "row-block-dataflow" : "launch-per-step-graph",
              c->strict ? "strict" : "fast",
              c->nslabs, c->size, s.plan.num_ctas, c->threads, s.plan.num_tasks, s.plan.tpr, c->engine == 3 ? c->df_k : 0, s.plan.strips,
              100.0 * lbm::interior_fraction(s.plan));
@@ -1286,7 +1285,7 @@ static int run_dataflow(lbm_ctx* c, int iters)
         unsigned base = c->base;
         void* args[] = {(void*)&s.dev, (void*)&par0, (void*)&step0, (void*)&it, (void*)&base};
         if (c->engine == 4) {
-            CK(cudaLaunchCooperativeKernel(narrow_fn(c->strict, ring), dim3(s.plan.rows * (c->prm.nx / 32)), dim3(32), args, 0, s.stream));
+            CK(cudaLaunchCooperativeKernel(row_fn(c->strict, ring), dim3(s.plan.rows), dim3(c->prm.nx), args, 0, s.stream));
         } else {
             const int blocks = (s.plan.num_tasks + c->df_k - 1) / c->df_k;
             CK(cudaLaunchCooperativeKernel(dataflow_fn(c->strict, c->df_k > 1, ring), dim3(blocks), dim3(32), args, 0, s.stream));

@@ -695,35 +695,46 @@ __global__ void __launch_bounds__(32, 16) lbm_dataflow_kernel(SlabDev d, int par
 }
 
 // ------------------------------------------------------------------------------------------
-// Engine 4: narrow dataflow - ONE CELL PER LANE.  Same protocol as engine 3, but a task is 32 consecutive
-// cells of a row and a record {a,b,c,tag} holds the three populations of ONE cell of a group, so a lane's
-// whole input is three records (lanes 0 and 31 fetch three more for the cells west / east of the warp).
-// Why: on the check grids (128x128 ... 256x256) a timestep is one dependency chain - records visible in L2,
-// poll, collide, store - and a wide task puts ~950 instructions of ONE warp into it (four cells per lane,
-// issued by one scheduler).  With a quarter of the work per warp and four times the warps, the chain
-// carries ~300 instructions and the SM's four schedulers work on different tasks at once.  (A whole lattice
-// inside one thread-block cluster's shared memory - the other B200 option - is issue-bound instead: at most
-// 16 SMs for 128 tasks x 950 instructions = 1900 cycles per step at 4 IPC, no better than engine 3;
-// DSMEM latency, 215 cycles, is no shorter than an L2 hit, 234-262)
-// nx must be a multiple of 32; at most one task per resident warp (lbm_create falls back to engine 3 / 1).
+// Engine 4: row blocks - one CTA per lattice ROW, one cell per thread (nx <= 1024, nx % 32 == 0).
+// Engine 3 pays, per timestep, one producer->consumer hop through L2 (530-1300 cycles one way, measured:
+// tools/probes/hop_probe.cu) PLUS the collide chain of the consuming warp (1460 cycles for four cells per lane:
+// tools/probes/df_split.py).  Cutting the tasks into independent 32-cell warps (one cell per lane, a record per cell)
+// was built and measured first and gained nothing (128x128: 1.50 vs 1.52 us per step, 256x256: 1.77 vs 1.65): every
+// such task waits for EIGHT other warps instead of two, and each extra neighbour adds its jitter.  Here a row is the
+// unit of the dataflow - it only ever waits for the row below and the row above - while its work is spread over
+// nx/32 warps on all four schedulers of the SM:
+//   * f0 stays in a register; f1 / f3 move one cell along the row by warp shuffle, across warp boundaries through
+//     a few words of shared memory: the horizontal record group of engines 3 / 4 never touches memory;
+//   * the northbound (f2,f5,f6) and southbound (f4,f7,f8) populations go to the rows above / below as ONE tagged
+//     16-byte record {a,b,c,tag} per cell and group; a thread polls exactly two records per step, and
+//     the elements beyond a warp's 32 cells also come through shared memory from the warp that polled them;
+//   * one __syncthreads per step (shared-memory words double-buffered by step parity), no flag, no fence.
+// Row slabs on several GPUs (RING): the edge rows' records go straight into the ring neighbour's record lattice,
+// exactly as in engine 3.
+// (A whole lattice inside one thread-block cluster's shared memory - the other B200 option - is issue-bound instead:
+// at most 16 SMs for 128 tasks x 950 instructions = 1900 cycles per step at 4 IPC, no better than engine 3, and four
+// times that on 256x256; DSMEM, 393-632 cycles per hop measured, only helps pairs inside one cluster.  DESIGN.md 4.6.)
 // ------------------------------------------------------------------------------------------
 template <bool S, bool RING>
-__global__ void __launch_bounds__(32, 24) lbm_narrow_kernel(SlabDev d, int par0, int step0, int iters, unsigned base)
+__global__ void __launch_bounds__(1024, 1) lbm_row_kernel(SlabDev d, int par0, int step0, int iters, unsigned base)
 {
+    // [parity][0: f1|f3 of the neighbouring cell, 1: its northbound element (f5|f6), 2: its southbound element (f8|f7)][warp]
+    __shared__ unsigned sm_w[2][3][kMaxWarps], sm_e[2][3][kMaxWarps];
+    __shared__ int sm_bail;
     const unsigned full = 0xffffffffu;
-    const int lane = threadIdx.x;
-    const int tpr = d.nx >> 5;
-    const int lr = blockIdx.x / tpr, x = (blockIdx.x % tpr) * 32 + lane;
-    const int nx = d.nx;
-    const bool edge = (lane == 0) || (lane == 31);
-    const int xx = (lane == 0) ? (x == 0 ? nx - 1 : x - 1) : (x == nx - 1 ? 0 : x + 1);   // the cell beyond the warp (edge lanes)
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    const int wnext = (warp + 1 == nw) ? 0 : warp + 1, wprev = (warp == 0) ? nw - 1 : warp - 1;    // periodic in x (d2q9-bgk.c:288-289)
+    const int lr = blockIdx.x, x = threadIdx.x;
     const bool blocked = (ld_mask(d.mask + ((unsigned)(lr + 1) * (unsigned)d.mask_pitch + ((unsigned)x >> 3))) >> (x & 7)) & 1u;
     const bool accel_row = (lr == d.accel_lr);
     const unsigned ps = (unsigned)d.ps;
-    const unsigned cell = (unsigned)(lr + 1) * (unsigned)nx + (unsigned)x;          // element offset in a SoA plane
+    const unsigned cell = (unsigned)(lr + 1) * (unsigned)d.nx + (unsigned)x;          // element offset in a SoA plane
     const int hs = rec_hrow_south<RING>(d, lr), hn = rec_hrow_north<RING>(d, lr);
+    if (threadIdx.x == 0) sm_bail = 0;
 
-    // ---- prologue: my cell of the SoA lattice -> records of parity step0 & 1 (after the first step's accelerate_flow)
+    // ---- prologue: my cell of the SoA lattice (after the first step's accelerate_flow); f0, f1, f3 stay here,
+    // the crossing populations go out as records of parity step0 & 1
+    float o0, o1, o3;
     {
         const float* src = d.buf[par0];
         float p[9];
@@ -733,52 +744,64 @@ __global__ void __launch_bounds__(32, 24) lbm_narrow_kernel(SlabDev d, int par0,
         const int rp0 = step0 & 1;
         st_record(rec_out_north<RING>(d, rp0, lr) + x, p[2], p[5], p[6], base + 1u);
         st_record(rec_out_south<RING>(d, rp0, lr) + x, p[4], p[7], p[8], base + 1u);
-        st_record(rec_group(d, rp0, lr + 1, kRecHorizontal) + x, p[0], p[1], p[3], base + 1u);
+        o0 = p[0]; o1 = p[1]; o3 = p[3];
+        if (lane == 31) sm_w[0][0][wnext] = __float_as_uint(o1);
+        if (lane == 0) sm_e[0][0][wprev] = __float_as_uint(o3);
     }
 
+    // the first poll of a step is issued at the end of the step before (behind its record stores), so that the
+    // loads are in flight while the warp reduces and stores the step's sum of |u|
+    uint4 N, Sg;
+    {
+        const int rp = step0 & 1;
+        N = ld_record(rec_group(d, rp, hs, kRecNorthbound) + x);
+        Sg = ld_record(rec_group(d, rp, hn, kRecSouthbound) + x);
+    }
     for (int s = 0; s < iters; ++s) {
         const unsigned tag = base + 1u + (unsigned)s;
-        const int rp = (step0 + s) & 1;            // continues across runs (see df_step)
-        const uint4* gh = rec_group(d, rp, lr + 1, kRecHorizontal);
-        const uint4* gn = rec_group(d, rp, hs, kRecNorthbound);      // the south row's northbound populations
-        const uint4* gs = rec_group(d, rp, hn, kRecSouthbound);      // the north row's southbound populations
-        uint4 H, N, Sg, Hx, Nx, Sx;
-        Hx = Nx = Sx = make_uint4(0u, 0u, 0u, tag);
+        const int rp = (step0 + s) & 1;            // record parity continues across runs (see df_step)
+        const int sp = s & 1;                      // shared-memory parity
+        const uint4* gn = rec_group(d, rp, hs, kRecNorthbound) + x;      // the south row's northbound populations
+        const uint4* gs = rec_group(d, rp, hn, kRecSouthbound) + x;      // the north row's southbound populations
         long long t0 = 0;
         for (int tries = 0;; ++tries) {
-            H = ld_record(gh + x); N = ld_record(gn + x); Sg = ld_record(gs + x);
-            if (edge) { Hx = ld_record(gh + xx); Nx = ld_record(gn + xx); Sx = ld_record(gs + xx); }
-            const bool ok = H.w == tag && N.w == tag && Sg.w == tag && Hx.w == tag && Nx.w == tag && Sx.w == tag;
-            if (__all_sync(full, ok)) break;
+            if (__all_sync(full, N.w == tag && Sg.w == tag)) break;
             if (tries == 0) t0 = clock64();
             const bool late = clock64() - t0 > kSpinLimitCycles;
             if (late) atomicExch(d.status, 2);
-            if (__any_sync(full, late || ld_status(d.status) != 0)) return;
+            if (__any_sync(full, late || ld_status(d.status) != 0)) { if (lane == 0) sm_bail = 1; break; }
+            N = ld_record(gn); Sg = ld_record(gs);
         }
+        // what the neighbouring warps need of my edge cells: f5 / f8 travel east (from my last cell), f6 / f7 west
+        if (lane == 31) { sm_w[sp][1][wnext] = N.y; sm_w[sp][2][wnext] = Sg.z; }
+        if (lane == 0) { sm_e[sp][1][wprev] = N.z; sm_e[sp][2][wprev] = Sg.y; }
+        __syncthreads();
+        if (sm_bail) return;                       // a neighbour never arrived (status is set): the whole row leaves together
         // pull (d2q9-bgk.c:315): f1,f5,f8 come from the west cell, f3,f6,f7 from the east cell
-        float p[9];
-        p[0] = __uint_as_float(H.x);
-        p[2] = __uint_as_float(N.x);
-        p[4] = __uint_as_float(Sg.x);
-        const unsigned w1 = __shfl_up_sync(full, H.y, 1), w5 = __shfl_up_sync(full, N.y, 1), w8 = __shfl_up_sync(full, Sg.z, 1);
-        const unsigned e3 = __shfl_down_sync(full, H.z, 1), e6 = __shfl_down_sync(full, N.z, 1), e7 = __shfl_down_sync(full, Sg.y, 1);
-        p[1] = __uint_as_float(lane == 0 ? Hx.y : w1);
-        p[5] = __uint_as_float(lane == 0 ? Nx.y : w5);
-        p[8] = __uint_as_float(lane == 0 ? Sx.z : w8);
-        p[3] = __uint_as_float(lane == 31 ? Hx.z : e3);
-        p[6] = __uint_as_float(lane == 31 ? Nx.z : e6);
-        p[7] = __uint_as_float(lane == 31 ? Sx.y : e7);
-
         float q[1][9];
-#pragma unroll
-        for (int k = 0; k < 9; ++k) q[0][k] = p[k];
+        const unsigned w1 = __shfl_up_sync(full, __float_as_uint(o1), 1), w5 = __shfl_up_sync(full, N.y, 1), w8 = __shfl_up_sync(full, Sg.z, 1);
+        const unsigned e3 = __shfl_down_sync(full, __float_as_uint(o3), 1), e6 = __shfl_down_sync(full, N.z, 1), e7 = __shfl_down_sync(full, Sg.y, 1);
+        q[0][0] = o0;
+        q[0][2] = __uint_as_float(N.x);
+        q[0][4] = __uint_as_float(Sg.x);
+        q[0][1] = __uint_as_float(lane == 0 ? sm_w[sp][0][warp] : w1);
+        q[0][5] = __uint_as_float(lane == 0 ? sm_w[sp][1][warp] : w5);
+        q[0][8] = __uint_as_float(lane == 0 ? sm_w[sp][2][warp] : w8);
+        q[0][3] = __uint_as_float(lane == 31 ? sm_e[sp][0][warp] : e3);
+        q[0][6] = __uint_as_float(lane == 31 ? sm_e[sp][1][warp] : e6);
+        q[0][7] = __uint_as_float(lane == 31 ? sm_e[sp][2][warp] : e7);
+
         const float usum = collide_n<S, 1>(q, blocked ? 1u : 0u, d.omega);
         const bool last = (s + 1 == iters);
         if (!last && accel_row) accelerate_cell(q[0], blocked, d.aw1, d.aw2);     // accelerate_flow for the next step
         if (!last) {
             st_record(rec_out_north<RING>(d, rp ^ 1, lr) + x, q[0][2], q[0][5], q[0][6], tag + 1u);
             st_record(rec_out_south<RING>(d, rp ^ 1, lr) + x, q[0][4], q[0][7], q[0][8], tag + 1u);
-            st_record(rec_group(d, rp ^ 1, lr + 1, kRecHorizontal) + x, q[0][0], q[0][1], q[0][3], tag + 1u);
+            o0 = q[0][0]; o1 = q[0][1]; o3 = q[0][3];
+            if (lane == 31) sm_w[sp ^ 1][0][wnext] = __float_as_uint(o1);
+            if (lane == 0) sm_e[sp ^ 1][0][wprev] = __float_as_uint(o3);
+            N = ld_record(rec_group(d, rp ^ 1, hs, kRecNorthbound) + x);      // next step's first poll
+            Sg = ld_record(rec_group(d, rp ^ 1, hn, kRecSouthbound) + x);
         } else {                                    // the run's result goes back to the SoA lattice
             float* dst = d.buf[par0 ^ (iters & 1)];
 #pragma unroll
@@ -786,8 +809,8 @@ __global__ void __launch_bounds__(32, 24) lbm_narrow_kernel(SlabDev d, int par0,
                 if (chk_ptr(dst + ((unsigned)k * ps + cell), 4)) dst[(unsigned)k * ps + cell] = q[0][k];
         }
         const double acc = warp_sum((double)usum);
-        if (lane == 0 && chk_ptr(d.partials + ((long long)(step0 + s) * d.num_ctas + blockIdx.x), 8))
-            d.partials[(long long)(step0 + s) * d.num_ctas + blockIdx.x] = acc;
+        const long long slot = (long long)(step0 + s) * d.num_ctas + (long long)blockIdx.x * nw + warp;
+        if (lane == 0 && chk_ptr(d.partials + slot, 8)) d.partials[slot] = acc;
     }
 }
 

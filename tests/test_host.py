@@ -198,7 +198,7 @@ def test_tagged_record_accesses_are_never_narrowed_in_sass(lib):
             fn = m.group(1)
             continue
         m = re.search(r"\b(LDG|STG)\.E((?:\.[A-Z0-9]+)*)\.STRONG\.SYS\b", line)
-        if m and fn and re.search(r"lbm_(persistent|dataflow|narrow|step)_kernel", fn):
+        if m and fn and re.search(r"lbm_(persistent|dataflow|row|step)_kernel", fn):
             per_fn.setdefault(fn, []).append(m.group(1) + m.group(2))
     assert per_fn, "no timestep kernels found in the SASS"
     total = 0
