@@ -503,11 +503,14 @@ int env_int(const char* name, int dflt)
 
 // Runs fn(begin, end) over [0, n) on a few host threads when the range is large (set-up work on the
 // 16384x1024 lattice: 16 M obstacle ints to count and pack; downloads of hundreds of MB).
+// In one-process-per-GPU mode the `sharers` ranks of a node do this at the same moment: each takes its share of the cores.
+std::atomic<int> g_host_sharers{1};
 template <class F>
 void host_parallel(size_t n, size_t grain, F fn)
 {
     unsigned hw = std::thread::hardware_concurrency();
-    size_t nt = std::min<size_t>(std::min<size_t>(hw ? hw : 1, 8), n / std::max<size_t>(grain, 1));
+    hw = std::max(1u, (hw ? hw : 1u) / (unsigned)std::max(1, g_host_sharers.load()));
+    size_t nt = std::min<size_t>(std::min<size_t>(hw, 8), n / std::max<size_t>(grain, 1));
     if (const char* e = getenv("LBM_HOST_THREADS")) nt = std::min<size_t>(nt, (size_t)std::max(1, atoi(e)));
     if (nt <= 1) { fn((size_t)0, n); return; }
     std::vector<std::thread> th;
@@ -1544,6 +1547,7 @@ int lbm_create_rank(lbm_ctx** out, const lbm_params* params, const int* obstacle
                     const lbm_options* opts)
 {
     lbm_ctx* c = nullptr;
+    if (size > 1) g_host_sharers = std::min(size, std::max(1, lbm_device_count()));   // ranks of this node set up side by side
     if (create_common(out, params, obstacles, opts, &c)) return 1;
     int rc = 0;
     if (size < 1 || size > params->ny || rank < 0 || rank >= size) rc = fail("bad rank %d / size %d", rank, size);
