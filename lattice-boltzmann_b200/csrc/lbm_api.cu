@@ -860,6 +860,20 @@ int slab_create(lbm_ctx* c, Slab& s, int rank, int device, const int* obst)
     return check_upload(device);
 }
 
+// The tagged halo records need a peer link on which a 16-byte store lands as one unit; that is established (stress test,
+// bit-exact tests) for NVLink / NVSwitch, which is also the only kind of link that reports native peer atomics.  A
+// PCIe peer-to-peer pair is refused unless LBM_ALLOW_ANY_PEER_LINK=1.
+int peer_link_unsuitable(int dev, int peer)
+{
+    if (dev == peer || env_int("LBM_ALLOW_ANY_PEER_LINK", 0)) return 0;
+    int native = 0;
+    if (cudaDeviceGetP2PAttribute(&native, cudaDevP2PAttrNativeAtomicSupported, dev, peer) != cudaSuccess) { cudaGetLastError(); native = 0; }
+    if (!native)
+        return fail("devices %d and %d are peers over a link without native atomics (not NVLink): the 16-byte tagged halo "
+                    "records are only validated over NVLink; set LBM_ALLOW_ANY_PEER_LINK=1 to run anyway", dev, peer);
+    return 0;
+}
+
 int count_cells(lbm_ctx* c, const int* obst)
 {
     const lbm_params& P = c->prm;
@@ -1155,6 +1169,7 @@ int lbm_create(lbm_ctx** out, const lbm_params* params, const int* obstacles, in
             int can = 0;
             cudaDeviceCanAccessPeer(&can, s.device, o->device);
             if (!can) { rc = fail("device %d cannot access peer %d", s.device, o->device); break; }
+            if (peer_link_unsuitable(s.device, o->device)) { rc = 1; break; }
             cudaError_t e = cudaDeviceEnablePeerAccess(o->device, 0);
             if (e == cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError();
             else if (e != cudaSuccess) { rc = fail("cudaDeviceEnablePeerAccess: %s", cudaGetErrorString(e)); break; }
@@ -1538,6 +1553,7 @@ int lbm_total_density(lbm_ctx* c, float* out)
 struct IpcBlob {
     unsigned magic;
     int rank, size, nx, rows, engine;
+    char bus_id[20];               // PCI bus id of the exporting rank's GPU (lets the importer vet the link)
     cudaIpcMemHandle_t ll_in;      // engine 1: inbound halo slots
     cudaIpcMemHandle_t rec;        // engines 3 / 4: the record lattice (its two haloed rows are written by the neighbours)
 };
@@ -1578,6 +1594,7 @@ int lbm_rank_export(lbm_ctx* c, void* blob)
     memset(&b, 0, sizeof(b));
     b.magic = 0x4C424D32u;  // "LBM2"
     b.rank = c->rank0; b.size = c->size; b.nx = c->prm.nx; b.rows = s.plan.rows; b.engine = c->engine;
+    CK(cudaDeviceGetPCIBusId(b.bus_id, (int)sizeof(b.bus_id), s.device));
     if (c->size > 1) { CK(cudaIpcGetMemHandle(&b.ll_in, s.ll_in)); mark_exported(s.ll_in); }
     if (c->size > 1 && s.rec) { CK(cudaIpcGetMemHandle(&b.rec, s.rec)); mark_exported(s.rec); }
     memset(blob, 0, LBM_IPC_BLOB_BYTES);
@@ -1602,6 +1619,13 @@ int lbm_rank_connect(lbm_ctx* c, const void* blob_up, const void* blob_down)
     if (up.nx != c->prm.nx || dn.nx != c->prm.nx) return fail("lbm_rank_connect: neighbour lattice width differs");
     if (up.engine != c->engine || dn.engine != c->engine)
         return fail("lbm_rank_connect: neighbours run engines %d / %d, this rank engine %d", up.engine, dn.engine, c->engine);
+    for (const IpcBlob* o : {&up, &dn}) {
+        int peer = -1;
+        char id[sizeof(o->bus_id) + 1] = {0};
+        memcpy(id, o->bus_id, sizeof(o->bus_id));
+        if (cudaDeviceGetByPCIBusId(&peer, id) != cudaSuccess) { cudaGetLastError(); continue; }   // not visible here: cannot vet
+        if (peer_link_unsuitable(s.device, peer)) return 1;
+    }
     const bool same = (r_up == r_dn);   // size == 2: both neighbours are the same process
     CK(ipc_open_cached(&s.ipc_ll_up, up.ll_in));
     if (same) s.ipc_ll_down = s.ipc_ll_up;
