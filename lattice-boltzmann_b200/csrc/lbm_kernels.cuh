@@ -749,14 +749,9 @@ __global__ void __launch_bounds__(1024, 1) lbm_row_kernel(SlabDev d, int par0, i
         if (lane == 0) sm_e[0][0][wprev] = __float_as_uint(o3);
     }
 
-    // How many polls of a step's two records are kept in flight, about an L2 round trip / kRowPolls apart: a poll that
-    // reaches L2 before the record does costs a full round trip before its retry can go out, so with one poll at a
-    // time a record is noticed, on average, half a round trip late.  (Issuing a step's first poll EARLY - behind the
-    // previous step's record stores - was measured and is slower: 128x128 1.31 vs 1.17 us per step.)
-#ifndef LBM_ROW_POLLS
-#define LBM_ROW_POLLS 1
-#endif
-    constexpr int kRowPolls = LBM_ROW_POLLS;
+    // (Measured and dropped, profiles/r02_small_lattice.md: issuing a step's first poll early, behind the previous step's
+    // record stores - 1.31 vs 1.17 us per step on 128x128; two to four polls in flight a fraction of an L2 round trip
+    // apart - 1.32 / 1.40 / 1.48 vs 1.14.)
     for (int s = 0; s < iters; ++s) {
         const unsigned tag = base + 1u + (unsigned)s;
         const int rp = (step0 + s) & 1;            // record parity continues across runs (see df_step)
@@ -764,40 +759,14 @@ __global__ void __launch_bounds__(1024, 1) lbm_row_kernel(SlabDev d, int par0, i
         const uint4* gn = rec_group(d, rp, hs, kRecNorthbound) + x;      // the south row's northbound populations
         const uint4* gs = rec_group(d, rp, hn, kRecSouthbound) + x;      // the north row's southbound populations
         uint4 N, Sg;
-        if (kRowPolls == 1) {
-            long long t0 = 0;
-            for (int tries = 0;; ++tries) {
-                N = ld_record(gn); Sg = ld_record(gs);
-                if (__all_sync(full, N.w == tag && Sg.w == tag)) break;
-                if (tries == 0) t0 = clock64();
-                const bool late = clock64() - t0 > kSpinLimitCycles;
-                if (late) atomicExch(d.status, 2);
-                if (__any_sync(full, late || ld_status(d.status) != 0)) { if (lane == 0) sm_bail = 1; break; }
-            }
-        } else {
-            // kRowPolls polls in flight: issue them staggered, then keep re-issuing the oldest as it comes back empty
-            uint4 Nq[kRowPolls], Sq[kRowPolls];
-#pragma unroll
-            for (int i = 0; i < kRowPolls; ++i) {
-                Nq[i] = ld_record(gn); Sq[i] = ld_record(gs);
-                if (i + 1 < kRowPolls) { const long long t = clock64(); while (clock64() - t < 600 / kRowPolls) {} }
-            }
-            const long long t0 = clock64();
-            bool found = false;
-            while (!found) {
-#pragma unroll
-                for (int i = 0; i < kRowPolls; ++i) {
-                    if (!found) {
-                        if (__all_sync(full, Nq[i].w == tag && Sq[i].w == tag)) { N = Nq[i]; Sg = Sq[i]; found = true; }
-                        else { Nq[i] = ld_record(gn); Sq[i] = ld_record(gs); }
-                    }
-                }
-                if (!found) {
-                    const bool late = clock64() - t0 > kSpinLimitCycles;
-                    if (late) atomicExch(d.status, 2);
-                    if (__any_sync(full, late || ld_status(d.status) != 0)) { if (lane == 0) sm_bail = 1; N = Nq[0]; Sg = Sq[0]; break; }
-                }
-            }
+        long long t0 = 0;
+        for (int tries = 0;; ++tries) {
+            N = ld_record(gn); Sg = ld_record(gs);
+            if (__all_sync(full, N.w == tag && Sg.w == tag)) break;
+            if (tries == 0) t0 = clock64();
+            const bool late = clock64() - t0 > kSpinLimitCycles;
+            if (late) atomicExch(d.status, 2);
+            if (__any_sync(full, late || ld_status(d.status) != 0)) { if (lane == 0) sm_bail = 1; break; }
         }
         // what the neighbouring warps need of my edge cells: f5 / f8 travel east (from my last cell), f6 / f7 west
         if (lane == 31) { sm_w[sp][1][wnext] = N.y; sm_w[sp][2][wnext] = Sg.z; }
