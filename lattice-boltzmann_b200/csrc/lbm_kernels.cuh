@@ -749,6 +749,9 @@ __global__ void __launch_bounds__(1024, 1) lbm_row_kernel(SlabDev d, int par0, i
         if (lane == 0) sm_e[0][0][wprev] = __float_as_uint(o3);
     }
 
+#ifdef LBM_DF_PROBE   // dev aid: poll cycles, extra polls, barrier wait, collide + record stores, accumulated in registers
+    long long pc0 = 0, pc1 = 0, pc2 = 0, pc3 = 0;
+#endif
     // (Measured and dropped, profiles/r02_small_lattice.md: issuing a step's first poll early, behind the previous step's
     // record stores - 1.31 vs 1.17 us per step on 128x128; two to four polls in flight a fraction of an L2 round trip
     // apart - 1.32 / 1.40 / 1.48 vs 1.14.)
@@ -760,7 +763,14 @@ __global__ void __launch_bounds__(1024, 1) lbm_row_kernel(SlabDev d, int par0, i
         const uint4* gs = rec_group(d, rp, hn, kRecSouthbound) + x;      // the north row's southbound populations
         uint4 N, Sg;
         long long t0 = 0;
+#ifdef LBM_DF_PROBE
+        const long long pr0 = clock_fenced();
+        int pr_tries = 0;
+#endif
         for (int tries = 0;; ++tries) {
+#ifdef LBM_DF_PROBE
+            pr_tries = tries;
+#endif
             N = ld_record(gn); Sg = ld_record(gs);
             if (__all_sync(full, N.w == tag && Sg.w == tag)) break;
             if (tries == 0) t0 = clock64();
@@ -771,7 +781,13 @@ __global__ void __launch_bounds__(1024, 1) lbm_row_kernel(SlabDev d, int par0, i
         // what the neighbouring warps need of my edge cells: f5 / f8 travel east (from my last cell), f6 / f7 west
         if (lane == 31) { sm_w[sp][1][wnext] = N.y; sm_w[sp][2][wnext] = Sg.z; }
         if (lane == 0) { sm_e[sp][1][wprev] = N.z; sm_e[sp][2][wprev] = Sg.y; }
+#ifdef LBM_DF_PROBE
+        const long long pr1 = clock_fenced();
+#endif
         __syncthreads();
+#ifdef LBM_DF_PROBE
+        const long long pr2 = clock_fenced();
+#endif
         if (sm_bail) return;                       // a neighbour never arrived (status is set): the whole row leaves together
         // pull (d2q9-bgk.c:315): f1,f5,f8 come from the west cell, f3,f6,f7 from the east cell
         float q[1][9];
@@ -802,10 +818,19 @@ __global__ void __launch_bounds__(1024, 1) lbm_row_kernel(SlabDev d, int par0, i
             for (int k = 0; k < 9; ++k)
                 if (chk_ptr(dst + ((unsigned)k * ps + cell), 4)) dst[(unsigned)k * ps + cell] = q[0][k];
         }
+#ifdef LBM_DF_PROBE
+        pc0 += pr1 - pr0; pc1 += pr_tries; pc2 += pr2 - pr1; pc3 += clock_fenced() - pr2;
+#endif
         const double acc = warp_sum((double)usum);
         const long long slot = (long long)(step0 + s) * d.num_ctas + (long long)blockIdx.x * nw + warp;
         if (lane == 0 && chk_ptr(d.partials + slot, 8)) d.partials[slot] = acc;
     }
+#ifdef LBM_DF_PROBE
+    if (d.prof && lane == 0) {
+        long long* o = d.prof + ((long long)blockIdx.x * nw + warp) * kMaxWarps * 4;
+        o[0] = pc0; o[1] = pc1; o[2] = pc2; o[3] = pc3;
+    }
+#endif
 }
 
 }  // namespace lbm
