@@ -699,8 +699,12 @@ int configure_engine(lbm_ctx* c, int device)
     if (warps_row > 0) CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ4, row_fn(c->strict, ring), c->prm.nx, 0));
     const long long warps3 = (long long)std::min(occ3, occ3m) * sms;
     const long long steps = std::max(c->prm.max_iters, 1);
-    const bool mem3 = tasks * steps * (long long)sizeof(double) <= (2LL << 30);
-    const bool mem4 = warps_row * steps * (long long)sizeof(double) <= (2LL << 30);
+    // one double per resident warp and step (a per-row fold inside engine 4 - one thread per step, or warp 0 every 64 steps
+    // from a shared-memory ring - was measured: +0.1 us per step on 128x128 and 256x256, so the sums stay per warp): up to
+    // 8 GiB of the 180 GB (256x256 x 80 000 steps = 1.3 GB)
+    const long long partial_limit = 8LL << 30;
+    const bool mem3 = tasks * steps * (long long)sizeof(double) <= partial_limit;
+    const bool mem4 = warps_row * steps * (long long)sizeof(double) <= partial_limit;
     const bool fits4 = occ4 > 0 && rows_max <= (long long)occ4 * sms && mem4;
     // engine 3: a warp owns 1 task, or several consecutive ones when the slab has more tasks than resident warps.
     // Measured (profiles/r01_small_lattice.md): 2 per warp beats engine 1 by 2.3x (1024x512), 3 per warp by 1.4x
@@ -712,13 +716,13 @@ int configure_engine(lbm_ctx* c, int device)
     if (c->engine == 3) {
         const int k = std::max(k_min, env_int("LBM_DF_TASKS_PER_WARP", 1));
         if (!mem3 || k > 8)
-            return fail("engine 3 needs slabs of at most %lld warp-tasks (the largest here has %lld) and at most 2 GiB of "
+            return fail("engine 3 needs slabs of at most %lld warp-tasks (the largest here has %lld) and at most 8 GiB of "
                         "per-step partial sums", 8 * warps3, tasks);
         c->df_k = k;
     }
     if (c->engine == 4 && !fits4)
         return fail("engine 4 (one CTA per row) needs nx %% 32 == 0, nx <= 1024, slabs of at most %lld rows (the largest here "
-                    "has %d) and at most 2 GiB of per-step partial sums", (long long)occ4 * sms, rows_max);
+                    "has %d) and at most 8 GiB of per-step partial sums", (long long)occ4 * sms, rows_max);
     // auto: the row engine where it measured faster than engine 3 (rows of up to 256 cells: 128x128 1.17 vs 1.58 us per
     // step, 256x256 1.52 vs 1.68; 512x256 loses, 2.34 vs 2.16 - profiles/r02_small_lattice.md), then engine 3, then 1
     if (c->engine == 0) c->engine = (fits4 && c->prm.nx <= 256) ? 4 : fits3 ? 3 : 1;
