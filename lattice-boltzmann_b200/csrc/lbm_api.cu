@@ -730,7 +730,7 @@ int configure_engine(lbm_ctx* c, int device)
     if (c->threads % 32 || c->threads < 32 || c->threads > 512) return fail("threads_per_cta must be a multiple of 32 in [32,512]");
     int per_sm = c->opt.ctas_per_sm ? c->opt.ctas_per_sm : env_int("LBM_CTAS_PER_SM", 2);
     // multi-slab: two halo stage buffers per warp in dynamic shared memory
-    c->stage_bytes = c->size > 1 ? (size_t)(c->threads / 32) * 2 * lbm::kStageRecords * sizeof(uint4) : 0;
+    c->stage_bytes = c->size > 1 ? (size_t)(c->threads / 32) * 2 * lbm::kStageSlot * sizeof(uint4) : 0;
     CK(cudaFuncSetAttribute(persistent_fn(c->strict, c->size > 1), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->stage_bytes));
     int occ = 0;
     CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, persistent_fn(c->strict, c->size > 1), c->threads, c->stage_bytes));

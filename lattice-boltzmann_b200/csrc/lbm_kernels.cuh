@@ -127,10 +127,26 @@ __device__ __forceinline__ void ll_prefetch(const SlabDev& d, int par, int2 td, 
     if (g.lr == 0) ll_addresses<0>(d, d.ll_in + ll_slot(d, par, 0), g, pq, pw, pe);
     else ll_addresses<1>(d, d.ll_in + ll_slot(d, par, 1), g, pq, pw, pe);
     const int Q = d.nx >> 2;
+#ifdef LBM_STAGE_BULK
+    // lane 0: the four record planes of the task (contiguous: lane l's records sit l records after lane 0's) and the
+    // west record; the lane holding the task's last cell: the east record.  All counted on the buffer's mbarrier.
+    void* bar = stage + kStageRecords;
+    const int lanes = min(32, (d.nx - td.y * 128) >> 2);           // a ragged last chunk has fewer active lanes
+    const bool east = g.need_e && g.active;
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // the buffer was last read through the generic proxy
+    if (lane == 0) {
+        stage_bar_expect(bar, 4u * 16u * (unsigned)lanes + 16u + 16u);
+#pragma unroll
+        for (int r = 0; r < 4; ++r) bulk_copy(stage + r * 32, pq + r * Q, 16u * (unsigned)lanes, bar);
+        bulk_copy(stage + 128, pw, 16u, bar);
+    }
+    if (east) bulk_copy(stage + 129, pe, 16u, bar);
+#else
 #pragma unroll
     for (int r = 0; r < 4; ++r) cp_async_record(stage + r * 32 + lane, pq + r * Q);
     if (g.need_w) cp_async_record(stage + 128, pw);
     if (g.need_e && g.active) cp_async_record(stage + 129, pe);
+#endif
 }
 
 // Takes a staged edge task out of shared memory; false if any tag is not `tag` yet.
@@ -153,7 +169,7 @@ __device__ __forceinline__ bool ll_take(const uint4* stage, const TaskGeom& g, i
 // beyond the edge is pulled from the inbound halo slots, which must carry `tag`; pushes carry tag + 1.
 template <bool S, bool RING>
 __device__ __forceinline__ float process_task(const SlabDev& d, int par, int2 td, int lane, bool epilogue_accel, unsigned tag,
-                                            const uint4* stage = nullptr, long long* ll_cycles = nullptr)
+                                            const uint4* stage = nullptr, long long* ll_cycles = nullptr, unsigned stage_parity = 0)
 {
     const TaskGeom g = task_geom<RING>(d, td, lane);
     const float* __restrict__ src = d.buf[par];
@@ -196,7 +212,11 @@ __device__ __forceinline__ float process_task(const SlabDev& d, int par, int2 td
         const long long t0 = ll_cycles ? clock64() : 0;
         bool staged = false;       // `stage`: this task's records were prefetched into shared memory
         if (stage) {
+#ifdef LBM_STAGE_BULK
+            stage_bar_wait((void*)(stage + kStageRecords), stage_parity);
+#else
             cp_async_wait_all_but_last();
+#endif
             staged = ll_s ? ll_take<0>(stage, g, lane, tag, sv, w5, e6) : ll_take<1>(stage, g, lane, tag, nv, w8, e7);
         }
         if (!staged) {
@@ -392,7 +412,12 @@ __global__ void __launch_bounds__(512, 1) lbm_persistent_kernel(SlabDev d, int p
     // edge tasks are staged one task ahead; a one-row slab needs both sides at once and just polls
     // (only the CTAs that own edge tasks carry the staging bookkeeping through their task loop)
     const bool staging = RING && d.rows > 1 && edge_end > n_int;
-    uint4* const my_stage = ll_stage + warp * 2 * kStageRecords;
+    uint4* const my_stage = ll_stage + warp * 2 * kStageSlot;
+    unsigned stage_phase = 0;                     // (bulk staging) bit b: parity the next wait on stage buffer b expects
+#ifdef LBM_STAGE_BULK
+    if (RING && lane < 2) stage_bar_init(my_stage + lane * kStageSlot + kStageRecords);
+    if (RING) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+#endif
     constexpr bool prof = PROF;               // LBM_PROFILE=1 runs the instantiation with cycle counters
     long long c_wait = 0, c_bar = 0, c_ll = 0;
     const long long c_begin = prof ? clock64() : 0;
@@ -421,10 +446,12 @@ __global__ void __launch_bounds__(512, 1) lbm_persistent_kernel(SlabDev d, int p
             if (staging) {
                 const int kn = k + nw;           // edge tasks sit at [n_int, edge_end) of the CTA's list
                 if (kn >= n_int && kn < edge_end) {
-                    ll_prefetch(d, par, __ldg(d.task_order + t_lo + kn), lane, my_stage + ((ord + 1) & 1) * kStageRecords);
+                    ll_prefetch(d, par, __ldg(d.task_order + t_lo + kn), lane, my_stage + ((ord + 1) & 1) * kStageSlot);
                     staged_next = true;
                 }
+#ifndef LBM_STAGE_BULK
                 cp_async_commit();               // one group per task, empty or not
+#endif
             }
             if (k >= n_int && !waited) {
                 const long long t0 = prof ? clock64() : 0;
@@ -433,8 +460,9 @@ __global__ void __launch_bounds__(512, 1) lbm_persistent_kernel(SlabDev d, int p
                 waited = true;
             }
             const int2 td = __ldg(d.task_order + t_lo + k);
-            acc += (double)process_task<S, RING>(d, par, td, lane, epi, target, staged ? my_stage + (ord & 1) * kStageRecords : nullptr,
-                                           prof ? &c_ll : nullptr);
+            acc += (double)process_task<S, RING>(d, par, td, lane, epi, target, staged ? my_stage + (ord & 1) * kStageSlot : nullptr,
+                                           prof ? &c_ll : nullptr, (stage_phase >> (ord & 1)) & 1u);
+            if (staged) stage_phase ^= 1u << (ord & 1);
             staged = staged_next;
         }
         acc = warp_sum(acc);
