@@ -726,9 +726,24 @@ int configure_engine(lbm_ctx* c, int device)
     // auto: the row engine where it measured faster than engine 3 (rows of up to 256 cells: 128x128 1.17 vs 1.58 us per
     // step, 256x256 1.52 vs 1.68; 512x256 loses, 2.34 vs 2.16 - profiles/r02_small_lattice.md), then engine 3, then 1
     if (c->engine == 0) c->engine = (fits4 && c->prm.nx <= 256) ? 4 : fits3 ? 3 : 1;
-    c->threads = c->opt.threads_per_cta ? c->opt.threads_per_cta : env_int("LBM_THREADS", 256);
+    c->threads = c->opt.threads_per_cta ? c->opt.threads_per_cta : env_int("LBM_THREADS", 0);
+    int per_sm = c->opt.ctas_per_sm ? c->opt.ctas_per_sm : env_int("LBM_CTAS_PER_SM", 0);
+    if (c->engine == 1 && c->threads == 0 && per_sm == 0 && c->size <= c->prm.ny) {
+        // CTA shape of the persistent kernel, by the share of INTERIOR tasks the planner reaches with two CTAs of 8 warps
+        // per SM on the largest slab.  Measured on 16 slab shapes (profiles/r02_cta_shape_sweep.md): below 35 % a CTA's
+        // patch is so thin that the flag waits dominate, and ONE CTA of 16 warps per SM - twice the tasks per patch - is
+        // faster (1024x1024 +3.5 %, 4096x256 +26 %, 8192x128 +17 %, the 8-GPU slabs of 16384x1024 +2.3 %, never slower);
+        // from 36 % up the two smaller CTAs win by 3-8 % (16384x1024, its 2- and 4-GPU slabs, 2048x1024, 1024x2048).
+        try {
+            const lbm::SlabPlan probe = lbm::make_plan(c->prm.nx, c->prm.ny, 0, c->size, sms * 2);
+            if (lbm::interior_fraction(probe) < 0.35) { c->threads = 512; per_sm = 1; }
+        } catch (const std::exception& e) {
+            return fail("%s", e.what());
+        }
+    }
+    if (c->threads == 0) c->threads = 256;
+    if (per_sm == 0) per_sm = 2;
     if (c->threads % 32 || c->threads < 32 || c->threads > 512) return fail("threads_per_cta must be a multiple of 32 in [32,512]");
-    int per_sm = c->opt.ctas_per_sm ? c->opt.ctas_per_sm : env_int("LBM_CTAS_PER_SM", 2);
     // multi-slab: two halo stage buffers per warp in dynamic shared memory
     c->stage_bytes = c->size > 1 ? (size_t)(c->threads / 32) * 2 * lbm::kStageSlot * sizeof(uint4) : 0;
     CK(cudaFuncSetAttribute(persistent_fn(c->strict, c->size > 1), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->stage_bytes));
