@@ -138,6 +138,19 @@ int lbm_av_velocity(lbm_ctx* ctx, float* out);
 /* total_density() (d2q9-bgk.c:680-696), the DEBUG conservation invariant. */
 int lbm_total_density(lbm_ctx* ctx, float* out);
 
+/* lbm_av_velocity and lbm_total_density in one call that ALLOCATES NOTHING (no cudaMalloc / cudaFree, no allocating
+ * library routine): for callers that cannot allocate - code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it.  This entry point has no counterpart in the reference.
+ * Its scratch (a pair of doubles per lattice row and the two totals) is a file-scope device array of fixed
+ * size, LBM_NOALLOC_MAX_ROWS rows per GPU = 256 KB, which every GPU that loads the library holds until the process
+ * exits; a context with more rows than that on one GPU is rejected with an error (use the two allocating calls, or
+ * more GPUs).  *av_velocity = mean |u| over unblocked cells (un-normalised sum in one-process-per-GPU mode, as
+ * lbm_av_velocity), *total_density = sum of all populations; either pointer may be NULL.  The sums are folded in a fixed
+ * order (deterministic).  Synchronises.  All calls on a GPU share the one array: calls that overlap on the same GPU
+ * (two contexts driven from two host threads) race - serialise them. */
+#define LBM_NOALLOC_MAX_ROWS 16384
+int lbm_diagnostics_noalloc(lbm_ctx* ctx, float* av_velocity, float* total_density);
+
 /* ---- introspection ------------------------------------------------------------ */
 
 int lbm_abi_version(void);

@@ -57,6 +57,7 @@ SYMBOLS = {
     "lbm_get_final_state": (ctypes.c_int, [_P, _P, _P, _P, _P]),
     "lbm_av_velocity": (ctypes.c_int, [_P, _FP]),
     "lbm_total_density": (ctypes.c_int, [_P, _FP]),
+    "lbm_diagnostics_noalloc": (ctypes.c_int, [_P, _FP, _FP]),
     "lbm_abi_version": (ctypes.c_int, []),
     "lbm_checked_build": (ctypes.c_int, []),
     "lbm_last_error": (ctypes.c_char_p, []),
@@ -269,6 +270,13 @@ class Lattice:
         v = ctypes.c_float()
         self._ck(self.lib.lbm_total_density(self._ctx, ctypes.byref(v)))
         return np.float32(v.value)
+
+    def diagnostics_noalloc(self):
+        """(av_velocity, total_density) through the entry point that allocates nothing (fixed 256 KB device scratch,
+        at most LBM_NOALLOC_MAX_ROWS = 16384 rows per GPU)."""
+        a, b = ctypes.c_float(), ctypes.c_float()
+        self._ck(self.lib.lbm_diagnostics_noalloc(self._ctx, ctypes.byref(a), ctypes.byref(b)))
+        return np.float32(a.value), np.float32(b.value)
 
     # -- introspection
     def last_run_ms(self):

@@ -1547,6 +1547,116 @@ static int diagnostics(lbm_ctx* c, double* sum_u, double* sum_rho)
     return 0;
 }
 
+// ---- allocation-free diagnostics (lbm_diagnostics_noalloc) -------------------------------------------------------
+// The same two sums as k_diagnostics (sum of |u| over free cells, sum of all populations), for callers that must not
+// allocate: the scratch - one pair of doubles per lattice row, then the two totals - is a file-scope device array of
+// fixed size instead of a cudaMalloc'ed buffer.  Every GPU that loads the library holds its own copy (256 KB) until exit.
+// In HOST code the array's name is only a stand-in: the device address is taken once per device with
+// cudaGetSymbolAddress, with that device current, and passed to the kernels.
+constexpr int kNoAllocMaxRows = LBM_NOALLOC_MAX_ROWS;
+static __device__ __align__(256) double g_noalloc_scratch[2 * kNoAllocMaxRows + 2];
+
+// one block per row: scratch[2*row] = sum of |u| over the row's free cells, scratch[2*row + 1] = sum of its populations
+static __global__ void k_diag_rows(SlabDev d, int par, double* scratch)
+{
+    __shared__ double sh[2][32];
+    const int lr = blockIdx.x;
+    double su = 0.0, sd = 0.0;
+    for (int x = threadIdx.x; x < d.nx; x += blockDim.x) {
+        const float* f = d.buf[par] + (long long)(lr + 1) * d.nx + x;
+        float q[9];
+#pragma unroll
+        for (int k = 0; k < 9; ++k) q[k] = f[k * d.ps];
+        float rho = 0.f;
+#pragma unroll
+        for (int k = 0; k < 9; ++k) rho = __fadd_rn(rho, q[k]);
+        sd += (double)rho;
+        if (!cell_blocked(d, lr + 1, x)) {
+            const float vx = __fdiv_rn(__fsub_rn(__fadd_rn(__fadd_rn(q[1], q[5]), q[8]), __fadd_rn(__fadd_rn(q[3], q[6]), q[7])), rho);
+            const float vy = __fdiv_rn(__fsub_rn(__fadd_rn(__fadd_rn(q[2], q[5]), q[6]), __fadd_rn(__fadd_rn(q[4], q[7]), q[8])), rho);
+            su += (double)__fsqrt_rn(__fadd_rn(__fmul_rn(vx, vx), __fmul_rn(vy, vy)));
+        }
+    }
+    su = lbm::warp_sum(su);
+    sd = lbm::warp_sum(sd);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane == 0) { sh[0][warp] = su; sh[1][warp] = sd; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double a = 0.0, b = 0.0;
+        for (int w = 0; w < (int)(blockDim.x >> 5); ++w) { a += sh[0][w]; b += sh[1][w]; }
+        scratch[2 * lr] = a;
+        scratch[2 * lr + 1] = b;
+    }
+}
+
+// one block: folds the `rows` pairs in a fixed order (deterministic) into scratch[2*kNoAllocMaxRows], [.. + 1]
+static __global__ void k_diag_fold(double* scratch, int rows)
+{
+    __shared__ double sh[2][256];
+    double a = 0.0, b = 0.0;
+    for (int r = threadIdx.x; r < rows; r += blockDim.x) { a += scratch[2 * r]; b += scratch[2 * r + 1]; }
+    sh[0][threadIdx.x] = a;
+    sh[1][threadIdx.x] = b;
+    __syncthreads();
+    for (int o = blockDim.x >> 1; o > 0; o >>= 1) {
+        if ((int)threadIdx.x < o) { sh[0][threadIdx.x] += sh[0][threadIdx.x + o]; sh[1][threadIdx.x] += sh[1][threadIdx.x + o]; }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) { scratch[2 * kNoAllocMaxRows] = sh[0][0]; scratch[2 * kNoAllocMaxRows + 1] = sh[1][0]; }
+}
+
+// device address of g_noalloc_scratch on `device` (which the caller has made current), looked up once per device
+static int noalloc_scratch(int device, double** out)
+{
+    static std::mutex mu;
+    static double* ptr[LBM_MAX_GPUS * 8] = {nullptr};
+    if (device < 0 || device >= (int)(sizeof(ptr) / sizeof(ptr[0]))) return fail("lbm_diagnostics_noalloc: device ordinal %d out of range", device);
+    std::lock_guard<std::mutex> g(mu);
+    if (!ptr[device]) {
+        double* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress((void**)&p, g_noalloc_scratch);
+        if (e != cudaSuccess || !p)
+            return fail("lbm_diagnostics_noalloc: cudaGetSymbolAddress(g_noalloc_scratch) on device %d: %s", device, cudaGetErrorString(e));
+        ptr[device] = p;
+    }
+    *out = ptr[device];
+    return 0;
+}
+
+int lbm_diagnostics_noalloc(lbm_ctx* c, float* av_velocity, float* total_density)
+{
+    if (!c || (!av_velocity && !total_density)) return fail("lbm_diagnostics_noalloc: bad arguments");
+    for (const Slab& s : c->slabs)
+        if (s.plan.rows > kNoAllocMaxRows)
+            return fail("lbm_diagnostics_noalloc: a slab of %d rows exceeds the fixed scratch of LBM_NOALLOC_MAX_ROWS = %d rows per GPU "
+                        "(a static 256 KB device array; use lbm_av_velocity / lbm_total_density, which allocate, or more GPUs)",
+                        s.plan.rows, kNoAllocMaxRows);
+    if (lbm_sync(c)) return 1;
+    double su = 0.0, sr = 0.0;
+    for (Slab& s : c->slabs) {
+        CK(cudaSetDevice(s.device));
+        double* scratch = nullptr;
+        if (noalloc_scratch(s.device, &scratch)) return 1;
+        // the array is shared by every call on this device and keeps the last call's contents: the entries this call
+        // reads are all rewritten by k_diag_rows first; the totals are cleared so that a failed launch cannot leave the
+        // previous call's result to be read back
+        CK(cudaMemsetAsync(scratch + 2 * kNoAllocMaxRows, 0, 2 * sizeof(double), s.stream));
+        k_diag_rows<<<s.plan.rows, 256, 0, s.stream>>>(s.dev, c->par, scratch);
+        k_diag_fold<<<1, 256, 0, s.stream>>>(scratch, s.plan.rows);
+        CK(cudaGetLastError());
+        double h[2];
+        CK(cudaMemcpyAsync(h, scratch + 2 * kNoAllocMaxRows, sizeof(h), cudaMemcpyDeviceToHost, s.stream));
+        CK(cudaStreamSynchronize(s.stream));
+        su += h[0];
+        sr += h[1];
+    }
+    const int cells = c->prm.nx * c->prm.ny - c->blocked_cells;               // as lbm_av_velocity (d2q9-bgk.c:480)
+    if (av_velocity) *av_velocity = c->rank_mode ? (float)su : (float)su / (float)cells;
+    if (total_density) *total_density = (float)sr;
+    return 0;
+}
+
 int lbm_av_velocity(lbm_ctx* c, float* out)
 {
     if (!c || !out) return fail("bad arguments");
