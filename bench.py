@@ -547,7 +547,10 @@ def main():
             for g in ("128x128", "256x256"):
                 also[g] = also_leg(lbm, torch, dist, scratch, g, rank, world, e2e=False,
                                    note="BASELINE.json check grid; small-lattice engine, latency-bound (L2-resident)")
-            also["cli"] = cli_leg(grid)
+            try:
+                also["cli"] = cli_leg(grid)
+            except Exception as e:      # e.g. the C driver was not built: the headline line must still be printed
+                also["cli"] = {"error": str(e)[:200]}
         elif world in (2, 4):
             head = {2: "4096x1024", 4: "8192x1024"}[world]
             also[head] = also_leg(lbm, torch, dist, scratch, head, rank, world,
