@@ -929,7 +929,7 @@ void describe(lbm_ctx* c)
              c->engine == 1 ? "persistent-neighbour-sync" : c->engine == 3 ? "dataflow-tagged-records"
              : c->engine == 4 ? "row-block-dataflow" : "launch-per-step-graph",
              c->strict ? "strict" : "fast",
-             c->nslabs, c->size, s.plan.num_ctas, c->threads, s.plan.num_tasks, s.plan.tpr, c->engine == 3 ? c->df_k : 0, s.plan.strips,
+             c->nslabs, c->size, c->engine == 4 ? s.plan.rows : s.plan.num_ctas, c->engine == 4 ? c->prm.nx : c->threads, s.plan.num_tasks, s.plan.tpr, c->engine == 3 ? c->df_k : 0, s.plan.strips,
              100.0 * lbm::interior_fraction(s.plan));
 }
 

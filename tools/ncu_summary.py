@@ -111,6 +111,10 @@ def launch_list(tag):
 
 def main():
     tag = sys.argv[1] if len(sys.argv) > 1 else "r01"
+    if len(sys.argv) > 2 and sys.argv[2] == "row":       # engine 4 captures of tools/profile_r02_row.sh only
+        for grid in ("128x128", "256x256"):
+            full_summary(tag, grid, 2000, kind="row", config="4:0:0:1")
+        return
     launch_list(tag)
     per = {}
     for grid, steps in (("16384x1024", 40), ("1024x1024", 300)):
