@@ -58,7 +58,11 @@ int default_edge_weight_16()
         const int v = atoi(e);
         if (v >= 16 && v <= 64) return v;
     }
-    return 24;   // an edge task costs about 1.5 ordinary ones (sweep: 16 -> 73.4, 20 -> 75.9, 24 -> 79.1, 28 -> 78.5, 32 -> 75.5 GLUPS/GPU)
+    // an edge task costs about 1.75 ordinary ones.  Round-1 kernel, 2 GPUs, 16384x128 per GPU: 16 -> 73.4, 20 -> 75.9, 24 -> 79.1,
+    // 28 -> 78.5, 32 -> 75.5 GLUPS/GPU.  Round-2 kernel (records pushed except on the last step, 16-warp CTAs on thin slabs), same
+    // shape, two passes: 24 -> 79.2, 26 -> 80.0, 28 -> 80.6, 30 -> 79.5, 32 -> 76.3; with 2 x 8-warp CTAs 24 -> 79.3, 28 -> 80.3;
+    // 16384x1024 on 8 GPUs: 24 -> 608.8, 28 -> 615.8 (profiles/r02_cta_shape_sweep.md)
+    return 28;
 }
 
 Layout make_layout(int tpr, int rows, int ctas, bool edge_rows, int edge_weight_16)
